@@ -1,0 +1,149 @@
+// Device-side building blocks shared by every heat2d kernel (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include "heat2d.h"
+#include "host_common.h"
+
+#define H2D_CUDA_TRY(expr)                                                              \
+  do {                                                                                  \
+    cudaError_t e__ = (expr);                                                           \
+    if (e__ != cudaSuccess)                                                             \
+      return h2d_fail(H2D_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), \
+                      __FILE__, __LINE__);                                              \
+  } while (0)
+
+// Launches are checked (the reference never calls cudaGetLastError,
+// grad1612_cuda_heat.cu:83-84).
+#define H2D_CHECK_LAUNCH(name)                                                         \
+  do {                                                                                 \
+    cudaError_t e__ = cudaGetLastError();                                              \
+    if (e__ != cudaSuccess)                                                            \
+      return h2d_fail(H2D_ECUDA, "launch of %s failed: %s", name, cudaGetErrorString(e__)); \
+  } while (0)
+
+namespace h2d {
+
+// Geometry + coefficients every kernel needs, passed by value (__grid_constant__).
+struct Geo {
+  int32_t nx, ny, x0, y0, rows, cols, halo_r, halo_c;
+  int64_t pitch;
+  // inclusive global range of cells that are updated; all others keep their value
+  int32_t ax_lo, ax_hi, ay_lo, ay_hi;
+  float a0, cx, cy;  // fp32 mode
+  double dcx, dcy;   // strict modes
+};
+
+inline Geo make_geo(const h2d_tile_t& t, const h2d_phys_t& p) {
+  Geo g;
+  g.nx = t.nx; g.ny = t.ny; g.x0 = t.x0; g.y0 = t.y0; g.rows = t.rows; g.cols = t.cols;
+  g.halo_r = t.halo_r; g.halo_c = t.halo_c; g.pitch = t.pitch;
+  if (p.boundary == H2D_BOUNDARY_FIXED) {
+    g.ax_lo = 1; g.ax_hi = t.nx - 2; g.ay_lo = 1; g.ay_hi = t.ny - 2;
+  } else {
+    g.ax_lo = 0; g.ax_hi = t.nx - 1; g.ay_lo = 0; g.ay_hi = t.ny - 1;
+  }
+  g.a0 = (float)(1.0 - 2.0 * p.cx - 2.0 * p.cy);
+  g.cx = (float)p.cx; g.cy = (float)p.cy;
+  g.dcx = p.cx; g.dcy = p.cy;
+  return g;
+}
+
+// ---------------------------------------------------------------- arithmetic
+// One point.  Must round exactly like point<ARITH>() in oracle.cpp.
+//   xm/xp: rows above/below, ym/yp: left/right (contiguous index).
+template <int ARITH>
+__device__ __forceinline__ float point(float c, float xm, float xp, float ym, float yp,
+                                       const Geo& g) {
+  const float ew = __fadd_rn(xp, xm);
+  const float ns = __fadd_rn(yp, ym);
+  if (ARITH == H2D_ARITH_FP32) {
+    return __fmaf_rn(g.cx, ew, __fmaf_rn(g.cy, ns, __fmul_rn(g.a0, c)));
+  } else {
+    const double dc = (double)c;
+    const double t1 = __fma_rn(-2.0, dc, (double)ew);  // exact product: same bits as ew - 2.0*c
+    const double t2 = __fma_rn(-2.0, dc, (double)ns);
+    double r;
+    if (ARITH == H2D_ARITH_STRICT_FMA) {
+      r = __fma_rn(g.dcy, t2, __fma_rn(g.dcx, t1, dc));
+    } else {
+      r = __dadd_rn(__dadd_rn(dc, __dmul_rn(g.dcx, t1)), __dmul_rn(g.dcy, t2));
+    }
+    return __double2float_rn(r);
+  }
+}
+
+// Four consecutive points of one row.  u/c/d = rows above / centre / below,
+// L = value left of c.x, R = value right of c.w.
+// fp32 mode uses the packed f32x2 pipe (FADD2/FMUL2/FFMA2 on sm_100a): two
+// points per instruction, IEEE round-to-nearest per element, so the result is
+// bit-identical to the scalar form.
+template <int ARITH>
+__device__ __forceinline__ float4 point4(const float4& u, const float4& c, const float4& d,
+                                         float L, float R, const Geo& g) {
+  float4 o;
+  if (ARITH == H2D_ARITH_FP32) {
+    const float2 a0 = make_float2(g.a0, g.a0), cx = make_float2(g.cx, g.cx),
+                 cy = make_float2(g.cy, g.cy);
+    const float2 ns01 = make_float2(__fadd_rn(c.y, L), __fadd_rn(c.z, c.x));
+    const float2 ns23 = make_float2(__fadd_rn(c.w, c.y), __fadd_rn(R, c.z));
+    const float2 g01 = __ffma2_rn(cy, ns01, __fmul2_rn(a0, make_float2(c.x, c.y)));
+    const float2 g23 = __ffma2_rn(cy, ns23, __fmul2_rn(a0, make_float2(c.z, c.w)));
+    const float2 ew01 = __fadd2_rn(make_float2(d.x, d.y), make_float2(u.x, u.y));
+    const float2 ew23 = __fadd2_rn(make_float2(d.z, d.w), make_float2(u.z, u.w));
+    const float2 o01 = __ffma2_rn(cx, ew01, g01);
+    const float2 o23 = __ffma2_rn(cx, ew23, g23);
+    o = make_float4(o01.x, o01.y, o23.x, o23.y);
+  } else {
+    o.x = point<ARITH>(c.x, u.x, d.x, L, c.y, g);
+    o.y = point<ARITH>(c.y, u.y, d.y, c.x, c.z, g);
+    o.z = point<ARITH>(c.z, u.z, d.z, c.y, c.w, g);
+    o.w = point<ARITH>(c.w, u.w, d.w, c.z, R, g);
+  }
+  return o;
+}
+
+// ------------------------------------------------------------------- helpers
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__device__ __forceinline__ uint64_t globaltimer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_sys_f32(float* p, float v) {
+  asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+
+// Spin until *flag >= want (wrap-safe) or the watchdog expires.  Returns false
+// on timeout.  One thread calls this; a dead peer must not hang the kernel
+// forever (failure detection).
+__device__ __forceinline__ bool wait_flag_ge(const uint32_t* flag, uint32_t want,
+                                             int64_t timeout_ns) {
+  if ((int32_t)(ld_acquire_sys(flag) - want) >= 0) return true;
+  const uint64_t t0 = globaltimer_ns();
+  for (;;) {
+    if ((int32_t)(ld_acquire_sys(flag) - want) >= 0) return true;
+    if ((int64_t)(globaltimer_ns() - t0) > timeout_ns) return false;
+    __nanosleep(64);
+  }
+}
+
+}  // namespace h2d

@@ -1,0 +1,689 @@
+// stencil_tk — the flagship kernel: K time steps per launch (temporal
+// blocking), input rows streamed by TMA into per-warp shared-memory rings,
+// K levels of the stencil pipelined in registers, output written once; the
+// same kernel stores the tile's edge bands straight into the neighbour GPUs'
+// ghost margins (peer memory over NVLink) and publishes one epoch flag per
+// launch, and optionally reduces the last sub-step's (new - old) for the
+// convergence test.
+//
+// What it replaces in the reference: the interior and edge sweeps
+// (grad1612_mpi_heat.c:239-259), the 16 persistent halo requests and their
+// Startall/Waitall (:210-235,244,274), the strided `column` datatype (:143),
+// the convergence loop and MPI_Allreduce (:262-271), and update<<<>>> of
+// grad1612_cuda_heat.cu:55-62.  None of that code is reused: the reference
+// exchanges one ghost cell per step, this kernel exchanges kmax-wide bands
+// once per K steps and never packs anything.
+//
+// Work decomposition.  One warp = one task = (strip, chunk):
+//   strip  128 consecutive columns (each lane owns 4 = one float4); the outer
+//          H = roundup4(K) columns on each side are the overlap whose results
+//          go stale as the K levels advance, the middle 128-2H are stored;
+//   chunk  R output rows; the warp streams R + 2K input rows top to bottom.
+// Each warp runs its own 4-stage TMA ring (no block-wide barrier in the loop).
+// Per input row the K levels advance by one row each; level t keeps two rows
+// (up, centre) in registers, so the state is 2*4*K floats per lane.
+#include <cuda.h>
+#include <cstdio>
+#include <cstring>
+#include <type_traits>
+#include <vector>
+#include "device_common.cuh"
+
+namespace h2d {
+
+constexpr int TK_W = 128;      // floats per strip row
+constexpr int TK_BR = 4;       // rows per TMA box
+constexpr int TK_STAGES = 4;   // boxes in flight per warp
+constexpr int TK_WARPS = 4;    // warps (tasks) per CTA
+constexpr int TK_STAGE_BYTES = TK_BR * TK_W * 4;
+constexpr int TK_SMEM_BYTES = TK_WARPS * TK_STAGES * TK_STAGE_BYTES + TK_WARPS * TK_STAGES * 8;
+constexpr int TK_KMAX = 8;
+
+struct PeerDev {
+  float* buf;       // neighbour's padded array that holds the SAME parity as our dst
+  uint32_t* flag;   // where we publish our epoch for that neighbour
+  int32_t x0, y0, halo_r, halo_c;
+  int64_t pitch;
+};
+
+struct TkArgs {
+  Geo g;
+  float* dst;
+  const int2* tasks;     // .x = strip | (comm_edge << 31), .y = chunk
+  int32_t n_tasks, n_chunks, chunk_rows, n_comm_edge;
+  int32_t H, wv, fw;     // column overlap, stored columns per strip, forwarded band width
+  int32_t has_peers;
+  PeerDev peer[H2D_NDIR];
+  const uint32_t* flags_in;
+  uint32_t epoch;
+  unsigned* edge_counter;
+  int32_t norm;
+  float* cta_partials;
+  unsigned* done_counter;
+  float* norm_out;
+  int64_t timeout_ns;
+  uint32_t* fault;
+};
+
+// ------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t"
+      "}" ::"r"(bar), "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1,
+                                            uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%2, %3}], [%4];" ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(addr));
+  return v;
+}
+
+// --------------------------------------------------- peer forwarding (cold)
+// Store the 4 just-computed values of owned row `rho`, columns j0..j0+3, into
+// every neighbour whose ghost margin contains them.  Called only by tasks that
+// touch the tile edge.  `smask` = which of the 4 elements are owned outputs.
+__device__ __noinline__ void forward_row(const TkArgs& a, int rho, int j0, float4 o, int smask) {
+  const int fw = a.fw;
+  const float v[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll 1
+  for (int d = 0; d < H2D_NDIR; ++d) {
+    const PeerDev& p = a.peer[d];
+    if (p.buf == nullptr) continue;
+    const int sx = (d == H2D_N || d == H2D_NW || d == H2D_NE) ? -1
+                 : (d == H2D_S || d == H2D_SW || d == H2D_SE) ? 1 : 0;
+    const int sy = (d == H2D_W || d == H2D_NW || d == H2D_SW) ? -1
+                 : (d == H2D_E || d == H2D_NE || d == H2D_SE) ? 1 : 0;
+    if (sx < 0 && rho >= fw) continue;
+    if (sx > 0 && rho < a.g.rows - fw) continue;
+    int m = 0;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int j = j0 + e;
+      const bool in = (sy == 0) || (sy < 0 ? j < fw : j >= a.g.cols - fw);
+      if (in && ((smask >> e) & 1)) m |= 1 << e;
+    }
+    if (m == 0) continue;
+    float* q = p.buf + (int64_t)(a.g.x0 + rho - p.x0 + p.halo_r) * p.pitch +
+               (a.g.y0 + j0 - p.y0 + p.halo_c);
+    if (m == 15 && (((uintptr_t)q) & 15) == 0) {
+      *reinterpret_cast<float4*>(q) = o;
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        if ((m >> e) & 1) q[e] = v[e];
+    }
+  }
+}
+
+// ------------------------------------------------------------- one task
+// FROZEN: the footprint contains cells that keep their value (global boundary
+// or outside the grid) -> per-element select.  EXTRAS: the task forwards rows
+// to neighbours and/or feeds the convergence norm.  Both are warp-uniform and
+// resolved at compile time so the common case (interior, no extras) carries
+// no overhead in its inner loop.
+template <int K, int ARITH, bool FROZEN, bool EXTRAS>
+__device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs& a, int strip,
+                                          int chunk, bool comm_edge, uint32_t ring,
+                                          uint32_t bars, int lane) {
+  const Geo& g = a.g;
+  const int R = a.chunk_rows;
+  const int r_lo = chunk * R;
+  const int r_hi = (chunk == a.n_chunks - 1) ? g.rows : r_lo + R;
+  const int n_out = r_hi - r_lo;
+  const int jbase = strip * a.wv - a.H;  // tile-local column of lane 0, element 0
+  const int j0 = jbase + lane * 4;
+  const int row0 = r_lo - K;             // first input row (tile-local)
+  const int n_in = n_out + 2 * K;
+  const int n_blk = (n_in + TK_BR - 1) / TK_BR;
+  const int tc0 = g.halo_c + jbase;      // TMA coordinates of the first box
+  const int tc1 = g.halo_r + row0;
+
+  // Which of my 4 columns are stored: inside the strip's valid window and owned.
+  const bool lane_in = (lane * 4 >= a.H) && (lane * 4 < TK_W - a.H);
+  int smask = 0;
+#pragma unroll
+  for (int e = 0; e < 4; ++e)
+    if (lane_in && (j0 + e) >= 0 && (j0 + e) < g.cols) smask |= 1 << e;
+  const bool st_full = smask == 15;
+  const bool st_part = smask != 0 && smask != 15;
+
+  bool act[4] = {true, true, true, true};
+  if (FROZEN) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int gy = g.y0 + j0 + e;
+      act[e] = gy >= g.ay_lo && gy <= g.ay_hi;
+    }
+  }
+
+  auto issue = [&](int b) {
+    const int s = b % TK_STAGES;
+    const uint32_t bar = bars + s * 8;
+    mbar_expect_tx(bar, TK_STAGE_BYTES);
+    tma_load_2d(ring + s * TK_STAGE_BYTES, tmap, tc0, tc1 + b * TK_BR, bar);
+  };
+  if (lane == 0) {
+    const int pre = n_blk < TK_STAGES ? n_blk : TK_STAGES;
+    for (int b = 0; b < pre; ++b) issue(b);
+  }
+
+  float4 st[K][2];
+#pragma unroll
+  for (int t = 0; t < K; ++t) st[t][0] = st[t][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+
+  float acc = 0.f;
+  // Level-K output of iteration i is tile-local row  row0 - K + i;  `ro` counts
+  // rows relative to r_lo so that "is an owned output row" is one unsigned compare.
+  int ro = -2 * K;
+  float* q = a.dst + (int64_t)(g.halo_r + r_lo - 2 * K) * g.pitch + g.halo_c + j0;
+
+  // One input row: advance all K levels.  P = which of the two state slots
+  // holds the "up" row this iteration (alternates every row).
+  auto row_step = [&](float4 down, auto Ptag) {
+    constexpr int P = decltype(Ptag)::value;
+    float4 cprev = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int t = 0; t < K; ++t) {
+      const float4 up = st[t][P];
+      const float4 c = st[t][P ^ 1];
+      const float L = __shfl_up_sync(0xffffffffu, c.w, 1);
+      const float Rn = __shfl_down_sync(0xffffffffu, c.x, 1);
+      float4 o = point4<ARITH>(up, c, down, L, Rn, g);
+      if (FROZEN) {
+        const int gx = g.x0 + r_lo + ro + (K - 1 - t);  // row of this level's output
+        const bool ract = gx >= g.ax_lo && gx <= g.ax_hi;
+        o.x = (ract && act[0]) ? o.x : c.x;
+        o.y = (ract && act[1]) ? o.y : c.y;
+        o.z = (ract && act[2]) ? o.z : c.z;
+        o.w = (ract && act[3]) ? o.w : c.w;
+      }
+      st[t][P] = down;
+      if (EXTRAS && t == K - 1) cprev = c;
+      down = o;
+    }
+    if ((unsigned)ro < (unsigned)n_out) {
+      if (st_full) {
+        *reinterpret_cast<float4*>(q) = down;
+      } else if (st_part) {
+        if (smask & 1) q[0] = down.x;
+        if (smask & 2) q[1] = down.y;
+        if (smask & 4) q[2] = down.z;
+        if (smask & 8) q[3] = down.w;
+      }
+      if (EXTRAS && smask != 0) {
+        if (comm_edge) forward_row(a, r_lo + ro, j0, down, smask);
+        if (a.norm != H2D_NORM_NONE) {
+          const float d0 = (smask & 1) ? down.x - cprev.x : 0.f;
+          const float d1 = (smask & 2) ? down.y - cprev.y : 0.f;
+          const float d2 = (smask & 4) ? down.z - cprev.z : 0.f;
+          const float d3 = (smask & 8) ? down.w - cprev.w : 0.f;
+          if (a.norm == H2D_NORM_L2SQ) {
+            acc = fmaf(d0, d0, acc); acc = fmaf(d1, d1, acc);
+            acc = fmaf(d2, d2, acc); acc = fmaf(d3, d3, acc);
+          } else {
+            acc = fmaxf(acc, fmaxf(fmaxf(fabsf(d0), fabsf(d1)), fmaxf(fabsf(d2), fabsf(d3))));
+          }
+        }
+      }
+    }
+    q += g.pitch;
+    ++ro;
+  };
+
+#pragma unroll 1
+  for (int b = 0; b < n_blk; ++b) {
+    const int s = b % TK_STAGES;
+    mbar_wait(bars + s * 8, (uint32_t)((b / TK_STAGES) & 1));
+    const uint32_t sbase = ring + s * TK_STAGE_BYTES + lane * 16;
+#pragma unroll 1
+    for (int rr = 0; rr < TK_BR; rr += 2) {
+      const float4 in0 = lds128(sbase + rr * (TK_W * 4));
+      const float4 in1 = lds128(sbase + (rr + 1) * (TK_W * 4));
+      row_step(in0, std::integral_constant<int, 0>{});
+      row_step(in1, std::integral_constant<int, 1>{});
+    }
+    // Everyone has read stage s: refill it with box b + STAGES.
+    __syncwarp();
+    if (lane == 0 && b + TK_STAGES < n_blk) issue(b + TK_STAGES);
+  }
+  return acc;
+}
+
+template <int K>
+struct TkBounds {
+  // K <= 5 fits 128 registers (4 CTAs = 16 warps per SM); deeper pipelines get
+  // 168 registers (3 CTAs = 12 warps) instead of spilling.
+  static constexpr int min_blocks = (K <= 5) ? 4 : 3;
+};
+
+template <int K, int ARITH>
+__global__ void __launch_bounds__(TK_WARPS * 32, TkBounds<K>::min_blocks)
+tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkArgs a) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ float cta_red[TK_WARPS];
+  __shared__ bool cta_last;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int task = (int)blockIdx.x * TK_WARPS + warp;
+  const uint32_t ring = smem_u32(smem) + warp * (TK_STAGES * TK_STAGE_BYTES);
+  const uint32_t bars = smem_u32(smem) + TK_WARPS * TK_STAGES * TK_STAGE_BYTES + warp * TK_STAGES * 8;
+
+  float acc = 0.f;
+  if (task < a.n_tasks) {
+    if (lane == 0) {
+#pragma unroll
+      for (int s = 0; s < TK_STAGES; ++s) mbar_init(bars + s * 8, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    const int2 tk = a.tasks[task];
+    const int strip = tk.x & 0x7fffffff;
+    const bool comm_edge = (tk.x < 0) && a.has_peers;
+    const int chunk = tk.y;
+
+    if (comm_edge) {
+      // Ghost cells of src were written by the neighbours' launch `epoch-1`;
+      // their ghost cells of OUR dst parity were last read by that launch too.
+      if (lane == 0) {
+        for (int d = 0; d < H2D_NDIR; ++d) {
+          if (a.peer[d].buf == nullptr) continue;
+          if (!wait_flag_ge(a.flags_in + d, a.epoch - 1u, a.timeout_ns)) atomicExch(a.fault, 1u + d);
+        }
+        asm volatile("fence.proxy.async;" ::: "memory");
+      }
+      __syncwarp();
+    }
+
+    // Does the footprint (all K levels) stay inside the updated region?
+    const Geo& g = a.g;
+    const int R = a.chunk_rows;
+    const int r_lo = chunk * R;
+    const int r_hi = (chunk == a.n_chunks - 1) ? g.rows : r_lo + R;
+    const int jb = strip * a.wv - a.H;
+    const bool frozen = (g.x0 + r_lo - K < g.ax_lo) || (g.x0 + r_hi - 1 + K > g.ax_hi) ||
+                        (g.y0 + jb < g.ay_lo) || (g.y0 + jb + TK_W - 1 > g.ay_hi);
+    const bool extras = comm_edge || a.norm != H2D_NORM_NONE;
+    if (extras) {
+      // Cold variants: one instantiation handles frozen and active footprints.
+      acc = run_task<K, ARITH, true, true>(&tmap, a, strip, chunk, comm_edge, ring, bars, lane);
+    } else if (frozen) {
+      acc = run_task<K, ARITH, true, false>(&tmap, a, strip, chunk, false, ring, bars, lane);
+    } else {
+      acc = run_task<K, ARITH, false, false>(&tmap, a, strip, chunk, false, ring, bars, lane);
+    }
+
+    if (comm_edge) {
+      // Make this warp's peer stores visible system-wide, then count it in; the
+      // last edge task of the launch publishes the epoch to every neighbour.
+      __threadfence_system();
+      __syncwarp();
+      if (lane == 0) {
+        const unsigned prev = atomicAdd(a.edge_counter, 1u);
+        if (prev == (unsigned)a.n_comm_edge - 1u) {
+          *a.edge_counter = 0u;
+          __threadfence_system();
+          for (int d = 0; d < H2D_NDIR; ++d)
+            if (a.peer[d].buf != nullptr) st_release_sys(a.peer[d].flag, a.epoch);
+        }
+      }
+    }
+  }
+
+  if (a.norm == H2D_NORM_NONE) return;
+  // Deterministic two-level reduction: warp -> CTA -> last CTA.
+  const bool l2 = a.norm == H2D_NORM_L2SQ;
+  acc = l2 ? warp_sum(acc) : warp_max(acc);
+  if (lane == 0) cta_red[warp] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float v = cta_red[0];
+    for (int w = 1; w < TK_WARPS; ++w) v = l2 ? v + cta_red[w] : fmaxf(v, cta_red[w]);
+    a.cta_partials[blockIdx.x] = v;
+    __threadfence();
+    cta_last = atomicAdd(a.done_counter, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!cta_last) return;
+  __threadfence();
+  float v = 0.f;
+  for (int i = threadIdx.x; i < (int)gridDim.x; i += TK_WARPS * 32) {
+    const float x = __ldcg(a.cta_partials + i);
+    v = l2 ? v + x : fmaxf(v, x);
+  }
+  v = l2 ? warp_sum(v) : warp_max(v);
+  __syncthreads();
+  if (lane == 0) cta_red[warp] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = cta_red[0];
+    for (int w = 1; w < TK_WARPS; ++w) t = l2 ? t + cta_red[w] : fmaxf(t, cta_red[w]);
+    *a.norm_out = t;
+    *a.done_counter = 0u;
+  }
+}
+
+typedef void (*tk_fn_t)(const CUtensorMap, const TkArgs);
+
+template <int ARITH>
+static tk_fn_t tk_pick_k(int k) {
+  switch (k) {
+    case 1: return tk_kernel<1, ARITH>;
+    case 2: return tk_kernel<2, ARITH>;
+    case 3: return tk_kernel<3, ARITH>;
+    case 4: return tk_kernel<4, ARITH>;
+    case 5: return tk_kernel<5, ARITH>;
+    case 6: return tk_kernel<6, ARITH>;
+    case 7: return tk_kernel<7, ARITH>;
+    case 8: return tk_kernel<8, ARITH>;
+    default: return nullptr;
+  }
+}
+static tk_fn_t tk_pick(int k, int arith) {
+  switch (arith) {
+    case H2D_ARITH_FP32: return tk_pick_k<H2D_ARITH_FP32>(k);
+    case H2D_ARITH_STRICT: return tk_pick_k<H2D_ARITH_STRICT>(k);
+    case H2D_ARITH_STRICT_FMA: return tk_pick_k<H2D_ARITH_STRICT_FMA>(k);
+    default: return nullptr;
+  }
+}
+
+}  // namespace h2d
+
+using namespace h2d;
+
+// ------------------------------------------------------------------ the plan
+struct TaskList {
+  int2* dev = nullptr;
+  int n_tasks = 0, n_strips = 0, n_comm_edge = 0;
+};
+
+struct h2d_plan {
+  h2d_plan_desc_t desc;
+  Geo geo;
+  CUtensorMap tmap[2];
+  int n_chunks = 0, chunk_rows = 0, fw = 0;
+  TaskList lists[TK_KMAX / 4 + 1];  // index H/4 (H = 4, 8)
+  void* scratch = nullptr;          // counters + partials
+  bool own_scratch = false;
+  int max_ctas = 0;
+  int64_t launches = 0;
+  int device = 0;
+  bool has_peers = false;
+};
+
+static inline int round_up4(int k) { return (k + 3) & ~3; }
+
+static int choose_chunk_rows(int rows, int cols, int kmax) {
+  // Enough tasks for several waves of 148 SMs x 16 warps, but chunks long
+  // enough that the 2K-row pipeline fill stays a few per cent.
+  const int n_strips = (cols + (TK_W - 2 * round_up4(kmax)) - 1) / (TK_W - 2 * round_up4(kmax));
+  int R = 256;
+  while (R > 32 && (int64_t)(rows / R) * n_strips < 4 * 148 * 16) R >>= 1;
+  if (R < kmax) R = kmax;
+  return R;
+}
+
+static void plan_counts(const h2d_tile_t* t, int kmax, int chunk_rows, int* n_chunks,
+                        int* max_tasks) {
+  int R = chunk_rows > 0 ? chunk_rows : choose_chunk_rows(t->rows, t->cols, kmax);
+  int nc = t->rows / R;
+  if (nc < 1) nc = 1;
+  *n_chunks = nc;
+  int mt = 0;
+  for (int H = 4; H <= round_up4(kmax); H += 4) {
+    const int wv = TK_W - 2 * H;
+    const int ns = (t->cols + wv - 1) / wv;
+    if (ns * nc > mt) mt = ns * nc;
+  }
+  *max_tasks = mt;
+}
+
+static size_t scratch_layout_bytes(int max_tasks) {
+  const size_t ctas = ((size_t)max_tasks + TK_WARPS - 1) / TK_WARPS;
+  return 256 + ctas * sizeof(float);
+}
+
+typedef CUresult (*encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                    const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static int make_tmap(CUtensorMap* out, float* base, const h2d_tile_t& t) {
+  static encode_tiled_fn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    H2D_CUDA_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr));
+    if (!p || qr != cudaDriverEntryPointSuccess)
+      return h2d_fail(H2D_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    fn = (encode_tiled_fn)p;
+  }
+  const cuuint64_t gdim[2] = {(cuuint64_t)t.pitch, (cuuint64_t)(t.rows + 2 * t.halo_r)};
+  const cuuint64_t gstride[1] = {(cuuint64_t)t.pitch * 4};
+  const cuuint32_t box[2] = {TK_W, TK_BR};
+  const cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return h2d_fail(H2D_ECUDA, "cuTensorMapEncodeTiled failed with %d", (int)r);
+  return H2D_OK;
+}
+
+static int build_task_list(h2d_plan* p, int H, TaskList* out) {
+  const h2d_tile_t& t = p->desc.tile;
+  const int wv = TK_W - 2 * H;
+  const int ns = (t.cols + wv - 1) / wv;
+  const int nc = p->n_chunks;
+  const int R = p->chunk_rows;
+  const int fw = p->fw;
+  std::vector<int2> edge, inner;
+  edge.reserve((size_t)2 * (ns + nc));
+  inner.reserve((size_t)ns * nc);
+  for (int c = 0; c < nc; ++c) {
+    const int r_lo = c * R, r_hi = (c == nc - 1) ? t.rows : r_lo + R;
+    const bool row_edge = r_lo < fw || r_hi > t.rows - fw;
+    for (int s = 0; s < ns; ++s) {
+      const int j_lo = s * wv, j_hi = (j_lo + wv < t.cols) ? j_lo + wv : t.cols;
+      const bool col_edge = j_lo < fw || j_hi > t.cols - fw;
+      if (row_edge || col_edge)
+        edge.push_back(make_int2((int)((unsigned)s | 0x80000000u), c));
+      else
+        inner.push_back(make_int2(s, c));
+    }
+  }
+  out->n_strips = ns;
+  out->n_comm_edge = (int)edge.size();
+  out->n_tasks = (int)(edge.size() + inner.size());
+  edge.insert(edge.end(), inner.begin(), inner.end());
+  H2D_CUDA_TRY(cudaMalloc(&out->dev, edge.size() * sizeof(int2)));
+  H2D_CUDA_TRY(cudaMemcpy(out->dev, edge.data(), edge.size() * sizeof(int2), cudaMemcpyHostToDevice));
+  return H2D_OK;
+}
+
+extern "C" {
+
+size_t h2d_plan_scratch_bytes(const h2d_tile_t* tile, int32_t kmax, int32_t chunk_rows) {
+  if (!tile || kmax < 1 || kmax > TK_KMAX || tile->rows < 1 || tile->cols < 1) return 0;
+  int nc, mt;
+  plan_counts(tile, kmax, chunk_rows, &nc, &mt);
+  return scratch_layout_bytes(mt);
+}
+
+void h2d_plan_destroy(h2d_plan_t* p) {
+  if (!p) return;
+  for (auto& l : p->lists)
+    if (l.dev) cudaFree(l.dev);
+  if (p->own_scratch && p->scratch) cudaFree(p->scratch);
+  delete p;
+}
+
+h2d_plan_t* h2d_plan_create(const h2d_plan_desc_t* d) {
+  if (!d) { h2d_fail(H2D_EINVAL, "h2d_plan_create: null desc"); return nullptr; }
+  const h2d_tile_t& t = d->tile;
+  if (h2d_check_tile(&t)) return nullptr;
+  if (!d->buf[0] || !d->buf[1]) { h2d_fail(H2D_EINVAL, "h2d_plan_create: null buffer"); return nullptr; }
+  if (d->kmax < 1 || d->kmax > TK_KMAX) {
+    h2d_fail(H2D_EINVAL, "h2d_plan_create: kmax %d outside [1, %d]", d->kmax, TK_KMAX);
+    return nullptr;
+  }
+  const int Hmax = round_up4(d->kmax);
+  if (t.halo_r < d->kmax || t.halo_c < Hmax || t.halo_c % 4 != 0 || t.pitch % 4 != 0) {
+    h2d_fail(H2D_EINVAL,
+             "h2d_plan_create: need halo_r >= kmax (%d), halo_c >= %d and a multiple of 4, pitch %% 4 == 0",
+             d->kmax, Hmax);
+    return nullptr;
+  }
+  if ((((uintptr_t)d->buf[0]) | ((uintptr_t)d->buf[1])) & 127) {
+    h2d_fail(H2D_EINVAL, "h2d_plan_create: buffers must be 128-byte aligned");
+    return nullptr;
+  }
+  if (d->phys.arith < H2D_ARITH_FP32 || d->phys.arith > H2D_ARITH_STRICT_FMA) {
+    h2d_fail(H2D_EINVAL, "h2d_plan_create: unknown arith %d", d->phys.arith);
+    return nullptr;
+  }
+  bool has_peers = false;
+  for (int k = 0; k < H2D_NDIR; ++k)
+    if (d->peer[k].buf[0] || d->peer[k].buf[1]) {
+      if (!d->peer[k].buf[0] || !d->peer[k].buf[1] || !d->peer[k].flag) {
+        h2d_fail(H2D_EINVAL, "h2d_plan_create: peer %d needs both buffers and a flag", k);
+        return nullptr;
+      }
+      has_peers = true;
+    }
+  if (has_peers && !d->flags_in) {
+    h2d_fail(H2D_EINVAL, "h2d_plan_create: peers given but flags_in is null");
+    return nullptr;
+  }
+  if (has_peers && (d->kmax > t.rows || d->kmax > t.cols)) {
+    h2d_fail(H2D_EINVAL, "h2d_plan_create: kmax %d exceeds the tile extent %dx%d", d->kmax, t.rows,
+             t.cols);
+    return nullptr;
+  }
+
+  h2d_plan* p = new h2d_plan();
+  p->desc = *d;
+  p->geo = make_geo(t, d->phys);
+  p->has_peers = has_peers;
+  cudaGetDevice(&p->device);
+  int max_tasks = 0;
+  plan_counts(&t, d->kmax, d->chunk_rows, &p->n_chunks, &max_tasks);
+  p->chunk_rows = d->chunk_rows > 0 ? d->chunk_rows : choose_chunk_rows(t.rows, t.cols, d->kmax);
+  if (p->n_chunks == 1) p->chunk_rows = t.rows;
+  p->fw = d->kmax;
+  if (p->fw > t.rows) p->fw = t.rows;
+  if (p->fw > t.cols) p->fw = t.cols;
+  p->max_ctas = (max_tasks + TK_WARPS - 1) / TK_WARPS;
+
+  if (make_tmap(&p->tmap[0], d->buf[0], t) || make_tmap(&p->tmap[1], d->buf[1], t)) {
+    delete p;
+    return nullptr;
+  }
+  for (int H = 4; H <= Hmax; H += 4)
+    if (build_task_list(p, H, &p->lists[H / 4])) {
+      h2d_plan_destroy(p);
+      return nullptr;
+    }
+  const size_t sb = scratch_layout_bytes(max_tasks);
+  if (d->scratch) {
+    p->scratch = d->scratch;
+  } else {
+    if (cudaMalloc(&p->scratch, sb) != cudaSuccess) {
+      h2d_fail(H2D_ENOMEM, "h2d_plan_create: cannot allocate %zu bytes of scratch", sb);
+      h2d_plan_destroy(p);
+      return nullptr;
+    }
+    p->own_scratch = true;
+  }
+  if (cudaMemset(p->scratch, 0, 256) != cudaSuccess) {
+    h2d_fail(H2D_ECUDA, "h2d_plan_create: cannot clear the scratch header");
+    h2d_plan_destroy(p);
+    return nullptr;
+  }
+  // Opt in to the dynamic shared memory size once per kernel variant.
+  for (int k = 1; k <= d->kmax; ++k) {
+    tk_fn_t fn = tk_pick(k, d->phys.arith);
+    cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, TK_SMEM_BYTES);
+  }
+  return p;
+}
+
+int h2d_plan_launch(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int norm, void* stream) {
+  if (!p) return h2d_fail(H2D_EINVAL, "h2d_plan_launch: null plan");
+  if (src_parity != 0 && src_parity != 1) return h2d_fail(H2D_EINVAL, "h2d_plan_launch: bad parity");
+  if (k < 1 || k > p->desc.kmax)
+    return h2d_fail(H2D_EINVAL, "h2d_plan_launch: k = %d outside [1, kmax = %d]", k, p->desc.kmax);
+  if (norm < H2D_NORM_NONE || norm > H2D_NORM_LINF)
+    return h2d_fail(H2D_EINVAL, "h2d_plan_launch: unknown norm %d", norm);
+  tk_fn_t fn = tk_pick(k, p->desc.phys.arith);
+  if (!fn) return h2d_fail(H2D_EINVAL, "h2d_plan_launch: no kernel for k = %d", k);
+  const int H = round_up4(k);
+  const TaskList& tl = p->lists[H / 4];
+
+  TkArgs a;
+  memset(&a, 0, sizeof a);
+  a.g = p->geo;
+  a.dst = p->desc.buf[1 - src_parity];
+  a.tasks = tl.dev;
+  a.n_tasks = tl.n_tasks;
+  a.n_chunks = p->n_chunks;
+  a.chunk_rows = p->chunk_rows;
+  a.n_comm_edge = tl.n_comm_edge;
+  a.H = H;
+  a.wv = TK_W - 2 * H;
+  a.fw = p->fw;
+  a.has_peers = p->has_peers ? 1 : 0;
+  for (int d = 0; d < H2D_NDIR; ++d) {
+    const h2d_peer_t& pr = p->desc.peer[d];
+    a.peer[d].buf = pr.buf[1 - src_parity];
+    a.peer[d].flag = pr.flag;
+    a.peer[d].x0 = pr.x0; a.peer[d].y0 = pr.y0;
+    a.peer[d].halo_r = pr.halo_r; a.peer[d].halo_c = pr.halo_c;
+    a.peer[d].pitch = pr.pitch;
+  }
+  a.flags_in = p->desc.flags_in;
+  a.epoch = epoch;
+  unsigned* hdr = (unsigned*)p->scratch;
+  a.edge_counter = hdr + 0;
+  a.done_counter = hdr + 1;
+  a.norm_out = (float*)(hdr + 2);
+  a.fault = hdr + 3;
+  a.cta_partials = (float*)((char*)p->scratch + 256);
+  a.norm = norm;
+  a.timeout_ns = p->desc.spin_timeout_ns > 0 ? p->desc.spin_timeout_ns : 10000000000LL;
+
+  const int grid = (tl.n_tasks + TK_WARPS - 1) / TK_WARPS;
+  fn<<<grid, TK_WARPS * 32, TK_SMEM_BYTES, (cudaStream_t)stream>>>(p->tmap[src_parity], a);
+  H2D_CHECK_LAUNCH("tk_kernel");
+  p->launches++;
+  return H2D_OK;
+}
+
+int64_t h2d_plan_launch_count(const h2d_plan_t* p) { return p ? p->launches : 0; }
+float* h2d_plan_norm_ptr(h2d_plan_t* p) { return p ? (float*)((unsigned*)p->scratch + 2) : nullptr; }
+uint32_t* h2d_plan_fault_ptr(h2d_plan_t* p) { return p ? (uint32_t*)p->scratch + 3 : nullptr; }
+
+}  // extern "C"

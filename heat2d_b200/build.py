@@ -1,0 +1,131 @@
+"""Build the two native libraries in-tree.
+
+    python -m heat2d_b200.build [--force] [--verbose]
+
+* ``_lib/libheat2d_cpu.so``  — oracle + dump writers, ``g++ -fopenmp -ffp-contract=off``
+* ``_lib/libheat2d_cuda.so`` — every CUDA kernel and the peer-memory runtime,
+  ``nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo`` (sm_100a only; nvcc
+  cross-compiles without a GPU).
+
+The ``.so`` files are git-ignored but travel to the GPU box with the snapshot.
+The reference has no build system at all (three command lines in readme.md:10-19).
+"""
+from __future__ import annotations
+
+import argparse
+import concurrent.futures as cf
+import os
+import shutil
+import subprocess
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+CSRC = ROOT / "csrc"
+INC = ROOT / "include"
+LIB = Path(__file__).resolve().parent / "_lib"
+OBJ = LIB / "obj"
+
+CPU_SOURCES = ["oracle.cpp", "dump.cpp"]
+CUDA_SOURCES = ["basic_kernels.cu", "stencil_tk.cu", "resident.cu", "peer.cu"]
+
+NVCC_FLAGS = [
+    "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
+    "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v",
+]
+CXX_FLAGS = ["-O3", "-std=c++17", "-fPIC", "-fopenmp", "-ffp-contract=off", "-Wall"]
+
+
+def _nvcc() -> str:
+    for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if cand and Path(cand).exists():
+            return cand
+    raise RuntimeError("nvcc not found")
+
+
+def _newer(target: Path, deps) -> bool:
+    if not target.exists():
+        return False
+    t = target.stat().st_mtime
+    return all(Path(d).stat().st_mtime <= t for d in deps)
+
+
+def _headers():
+    return list(CSRC.glob("*.h")) + list(CSRC.glob("*.cuh")) + list(INC.glob("*.h"))
+
+
+def _run(cmd, verbose, log_path=None):
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if log_path is not None:
+        Path(log_path).write_text(res.stdout + res.stderr)
+    if res.returncode != 0:
+        raise RuntimeError("build failed: %s\n%s\n%s" % (" ".join(map(str, cmd)), res.stdout, res.stderr))
+    if verbose:
+        sys.stderr.write(res.stdout + res.stderr)
+
+
+def build_cpu(force=False, verbose=False) -> Path:
+    LIB.mkdir(parents=True, exist_ok=True)
+    out = LIB / "libheat2d_cpu.so"
+    srcs = [CSRC / s for s in CPU_SOURCES]
+    if not force and _newer(out, srcs + _headers()):
+        return out
+    # Some images export CXX pointing at a g++ without libgomp; try the system
+    # compiler first and drop -fopenmp only as a last resort (the oracle then
+    # runs serially, results are identical).
+    cands = [c for c in ("/usr/bin/g++", os.environ.get("CXX"), shutil.which("g++")) if c]
+    errors = []
+    for flags in (CXX_FLAGS, [f for f in CXX_FLAGS if f != "-fopenmp"]):
+        for cxx in dict.fromkeys(cands):
+            cmd = [cxx, *flags, "-shared", f"-I{INC}", f"-I{CSRC}", *map(str, srcs), "-o", str(out)]
+            try:
+                _run(cmd, verbose)
+                return out
+            except RuntimeError as e:  # try the next compiler
+                errors.append(str(e))
+    raise RuntimeError("no working C++ compiler:\n" + "\n".join(errors))
+
+
+def build_cuda(force=False, verbose=False) -> Path:
+    LIB.mkdir(parents=True, exist_ok=True)
+    OBJ.mkdir(parents=True, exist_ok=True)
+    out = LIB / "libheat2d_cuda.so"
+    srcs = [CSRC / s for s in CUDA_SOURCES]
+    hdrs = _headers()
+    if not force and _newer(out, srcs + hdrs):
+        return out
+    nvcc = _nvcc()
+
+    def compile_one(src: Path) -> Path:
+        obj = OBJ / (src.stem + ".o")
+        if not force and _newer(obj, [src] + hdrs):
+            return obj
+        cmd = [nvcc, *NVCC_FLAGS, f"-I{INC}", f"-I{CSRC}", "-c", str(src), "-o", str(obj)]
+        _run(cmd, verbose, log_path=OBJ / (src.stem + ".ptxas.log"))
+        return obj
+
+    with cf.ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
+        objs = list(ex.map(compile_one, srcs))
+    cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", *map(str, objs), "-o", str(out)]
+    _run(cmd, verbose)
+    return out
+
+
+def build_all(force=False, verbose=False):
+    return build_cpu(force, verbose), build_cuda(force, verbose)
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
+    ap.add_argument("--force", action="store_true")
+    ap.add_argument("--verbose", action="store_true")
+    ap.add_argument("--cpu-only", action="store_true")
+    args = ap.parse_args(argv)
+    cpu = build_cpu(args.force, args.verbose)
+    print(cpu)
+    if not args.cpu_only:
+        print(build_cuda(args.force, args.verbose))
+
+
+if __name__ == "__main__":
+    main()

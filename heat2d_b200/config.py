@@ -1,0 +1,166 @@
+"""Run configuration: the reference's compile-time ``#define`` blocks as runtime options.
+
+Reference: ``grad1612_mpi_heat.c:5-21`` (NXPROB, NYPROB, STEPS, GRIDX, GRIDY,
+CONVERGENCE, INTERVAL, SENSITIVITY, CX, CY, DEBUG), ``grad1612_hybrid_heat.c:12-24``
+(NUMTHREADS), ``grad1612_cuda_heat.cu:6-13`` (BLOCKX/BLOCKY have no equivalent: the
+launch shape is fixed by the kernels), ``mpi_heat2Dn.c:29-44`` (float coefficients).
+"""
+from __future__ import annotations
+
+import dataclasses
+from dataclasses import dataclass
+from typing import Optional
+
+from ._native import ARITH, BOUNDARY, INIT, KMAX, NORM
+
+BACKENDS = ("fused", "single", "plain", "nccl-halo", "resident", "cpu")
+DUMPS = ("none", "prtdat", "rowmajor", "binary")
+CONV_MODES = ("exact", "fused-k")
+
+
+class ConfigError(ValueError):
+    pass
+
+
+@dataclass
+class HeatConfig:
+    """Everything a run needs.  Defaults are the reference's defaults."""
+
+    nx: int = 10                 # NXPROB: rows (slow index)
+    ny: int = 10                 # NYPROB: columns (contiguous index)
+    steps: int = 100             # STEPS
+    px: int = 1                  # GRIDX: tiles along x (rows)
+    py: int = 1                  # GRIDY: tiles along y (columns)
+    conv: bool = False           # CONVERGENCE
+    interval: int = 20           # INTERVAL
+    eps: float = 0.1             # SENSITIVITY
+    norm: str = "l2sq"           # l2sq = grad1612_mpi_heat.c:264-269; linf = north-star wording
+    conv_mode: str = "exact"     # exact: pre-step field + 0-based index, as the reference
+    cx: float = 0.1
+    cy: float = 0.1
+    cx_float: bool = False       # coefficients rounded to float first (mpi_heat2Dn.c:41-44)
+    boundary: str = "fixed"      # fixed | ghost-ring
+    arith: str = "fp32"          # fp32 | strict | strict-fma
+    init: str = "exact"          # ref-int32 | ref-uint32 | exact | zero
+    k: int = 8                   # time steps per launch / per halo exchange
+    backend: str = "fused"
+    halo: int = 8                # ghost depth of the tile arrays (>= k)
+    chunk_rows: int = 0          # 0 = let the plan choose
+    uneven: bool = True          # allow non-divisible splits (mpi_heat2Dn.c:89-116 style)
+    dump: str = "none"
+    out_dir: str = "."
+    threads: int = 1             # CPU backend only (NUMTHREADS)
+    debug: bool = False
+    restart: Optional[str] = None
+    start_step: int = 0
+    ref_conv_bug: bool = False   # replay the stale-`i` predicate of grad1612_mpi_heat.c:263
+    spin_timeout_s: float = 10.0
+
+    def validate(self, world_size: Optional[int] = None) -> "HeatConfig":
+        if self.nx < 1 or self.ny < 1:
+            raise ConfigError(f"grid {self.nx}x{self.ny} is empty")
+        if self.steps < 0:
+            raise ConfigError("steps must be >= 0")
+        if self.px < 1 or self.py < 1:
+            raise ConfigError("px and py must be >= 1")
+        if self.px > self.nx or self.py > self.ny:
+            raise ConfigError(f"process grid {self.px}x{self.py} has more tiles than grid lines")
+        if world_size is not None and self.backend not in ("single", "resident", "cpu"):
+            if self.px * self.py != world_size:
+                # grad1612_mpi_heat.c:55-58
+                raise ConfigError(
+                    f"ERROR: the number of tasks must be equal to {self.px * self.py}.")
+        if not self.uneven and (self.nx % self.px or self.ny % self.py):
+            # grad1612_mpi_heat.c:60-63
+            raise ConfigError(
+                f"ERROR: ({self.nx}/{self.px}) or ({self.ny}/{self.py}) is not an integer")
+        for name, table in (("boundary", BOUNDARY), ("arith", ARITH), ("init", INIT), ("norm", NORM)):
+            if getattr(self, name) not in table:
+                raise ConfigError(f"{name} must be one of {sorted(table)}")
+        if self.backend not in BACKENDS:
+            raise ConfigError(f"backend must be one of {BACKENDS}")
+        if self.dump not in DUMPS:
+            raise ConfigError(f"dump must be one of {DUMPS}")
+        if self.conv_mode not in CONV_MODES:
+            raise ConfigError(f"conv_mode must be one of {CONV_MODES}")
+        if not 1 <= self.k <= KMAX:
+            raise ConfigError(f"k must be in [1, {KMAX}]")
+        if self.halo < self.k:
+            raise ConfigError("halo must be >= k")
+        if self.conv and self.interval < 1:
+            raise ConfigError("interval must be >= 1")
+        if self.threads < 1:
+            raise ConfigError("threads must be >= 1")
+        return self
+
+    @property
+    def cx_eff(self) -> float:
+        """Coefficient as the double the arithmetic uses."""
+        import numpy as np
+        return float(np.float32(self.cx)) if self.cx_float else float(self.cx)
+
+    @property
+    def cy_eff(self) -> float:
+        import numpy as np
+        return float(np.float32(self.cy)) if self.cx_float else float(self.cy)
+
+    def replace(self, **kw) -> "HeatConfig":
+        return dataclasses.replace(self, **kw)
+
+    def to_dict(self) -> dict:
+        return dataclasses.asdict(self)
+
+
+@dataclass(frozen=True)
+class Launch:
+    """One kernel launch of the schedule: `k` steps; `check` = evaluate the
+    convergence norm on its last sub-step."""
+    k: int
+    check: bool
+    first_step: int  # 0-based index of the first step this launch performs
+
+
+def make_schedule(steps: int, k: int, conv: bool = False, interval: int = 20,
+                  conv_mode: str = "exact", start_step: int = 0):
+    """Split `steps` time steps into launches of at most `k` steps.
+
+    Convergence is evaluated on 0-based step indices that are multiples of
+    `interval` (the intent of ``grad1612_mpi_heat.c:263``).  In ``exact`` mode the
+    checked step is always its own k=1 launch, so that on convergence the
+    pre-step field is still intact in the source buffer (the reference breaks
+    out of the loop before flipping buffers, ``:269-273``).  In ``fused-k`` mode
+    the check rides on the last sub-step of a k-step launch.
+    """
+    out = []
+    s = start_step
+    end = start_step + steps
+    while s < end:
+        if conv:
+            nxt = ((s + interval - 1) // interval) * interval  # next checked index >= s
+            if conv_mode == "exact":
+                if nxt == s:
+                    out.append(Launch(1, True, s))
+                    s += 1
+                    continue
+                kk = min(k, nxt - s, end - s)
+                out.append(Launch(kk, False, s))
+                s += kk
+            else:
+                # a launch must END with the checked step (index nxt)
+                if nxt >= end:
+                    kk = min(k, end - s)
+                    out.append(Launch(kk, False, s))
+                    s += kk
+                    continue
+                n = nxt - s + 1
+                while n > k:
+                    out.append(Launch(k, False, s))
+                    s += k
+                    n -= k
+                out.append(Launch(n, True, s))
+                s += n
+        else:
+            kk = min(k, end - s)
+            out.append(Launch(kk, False, s))
+            s += kk
+    return out

@@ -1,0 +1,373 @@
+"""The heat-diffusion model: tile storage, per-tile engine, single-process solver.
+
+``Heat2DSolver`` is the public entry point a user of the reference switches to:
+it plays the role of ``main()`` in all four reference programs
+(``grad1612_mpi_heat.c:27-316``, ``grad1612_cuda_heat.cu:64-94``,
+``mpi_heat2Dn.c:46-218``): allocate, initialise, (dump), timed step loop with
+optional convergence test, (dump).  In one process it drives either one tile
+(``px = py = 1``) or P x Q *virtual tiles* on one GPU — the same kernels, flag
+protocol and peer stores as the multi-GPU path, pointed at local buffers and
+issued rank after rank on one stream.  The one-process-per-GPU version is
+:class:`heat2d_b200.parallel.dist.DistributedHeat2DSolver`.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+
+from .. import _native as N
+from ..config import HeatConfig, Launch, make_schedule
+from ..ops import kernels as K
+from ..parallel.decomp import Decomposition, OPPOSITE, TileSpec
+
+COL_MARGIN = 32  # floats; keeps owned column 0 128-byte aligned and >= roundup4(KMAX)
+
+
+def _round_up(v: int, m: int) -> int:
+    return (v + m - 1) // m * m
+
+
+def padded_geometry(spec: TileSpec, nx: int, ny: int, halo: int) -> N.Tile:
+    halo_c = max(COL_MARGIN, _round_up(halo, 4))
+    pitch = _round_up(spec.cols + 2 * halo_c, 32)
+    return N.Tile(nx, ny, spec.x0, spec.y0, spec.rows, spec.cols, halo, halo_c, pitch)
+
+
+def padded_bytes(tile: N.Tile) -> int:
+    return (tile.rows + 2 * tile.halo_r) * tile.pitch * 4
+
+
+class RawCudaArray:
+    """Expose a raw device address to torch through __cuda_array_interface__."""
+
+    def __init__(self, ptr: int, shape, typestr: str, owner=None):
+        self._owner = owner
+        self.__cuda_array_interface__ = {
+            "shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False),
+            "version": 2, "strides": None,
+        }
+
+
+def tensor_from_ptr(ptr: int, shape, dtype: torch.dtype, device, owner=None) -> torch.Tensor:
+    typestr = {torch.float32: "<f4", torch.int32: "<i4", torch.uint8: "|u1", torch.int64: "<i8"}[dtype]
+    return torch.as_tensor(RawCudaArray(ptr, shape, typestr, owner), device=device)
+
+
+class TileField:
+    """Double-buffered padded storage of one tile.
+
+    ``buf[p]`` has shape ``(rows + 2*halo_r, pitch)``; ``owned(p)`` is the strided
+    view of the cells this tile owns.  Margins are ghost cells (neighbour data
+    or zeros outside the grid) — the k-wide successor of the 1-cell ghost ring
+    of ``grad1612_mpi_heat.c:47-52,150-161``.
+    """
+
+    def __init__(self, spec: TileSpec, nx: int, ny: int, halo: int, device,
+                 storage: Optional[List[torch.Tensor]] = None):
+        self.spec = spec
+        self.tile = padded_geometry(spec, nx, ny, halo)
+        self.device = torch.device(device)
+        shape = (spec.rows + 2 * halo, self.tile.pitch)
+        if storage is None:
+            self.buf = [torch.zeros(shape, dtype=torch.float32, device=self.device) for _ in range(2)]
+        else:
+            self.buf = storage
+            for b in self.buf:
+                assert tuple(b.shape) == shape and b.dtype == torch.float32 and b.is_contiguous()
+
+    def owned(self, parity: int) -> torch.Tensor:
+        t = self.tile
+        return self.buf[parity][t.halo_r:t.halo_r + t.rows, t.halo_c:t.halo_c + t.cols]
+
+    def padded_window(self):
+        """Global index ranges covered by the padded array, clipped to the grid:
+        (gx0, gx1, gy0, gy1, local row offset, local col offset)."""
+        t = self.tile
+        gx0, gx1 = max(0, t.x0 - t.halo_r), min(t.nx, t.x0 + t.rows + t.halo_r)
+        gy0, gy1 = max(0, t.y0 - t.halo_c), min(t.ny, t.y0 + t.cols + t.halo_c)
+        return gx0, gx1, gy0, gy1, gx0 - (t.x0 - t.halo_r), gy0 - (t.y0 - t.halo_c)
+
+    def load_from_global(self, grid: torch.Tensor, parity: int = 0):
+        """Copy this tile's part of a full host/device grid, ghosts included."""
+        gx0, gx1, gy0, gy1, r0, c0 = self.padded_window()
+        self.buf[parity].zero_()
+        src = grid[gx0:gx1, gy0:gy1]
+        self.buf[parity][r0:r0 + (gx1 - gx0), c0:c0 + (gy1 - gy0)].copy_(src, non_blocking=True)
+
+
+@dataclass
+class RunResult:
+    steps_done: int            # number of updates applied to the returned field
+    iterations: int            # what the reference prints as "Exiting after %d iterations"
+    converged: bool
+    last_norm: float
+    elapsed_s: float           # device time of the step loop (max over ranks when distributed)
+    launches: int
+    checks: int
+    nx: int
+    ny: int
+
+    @property
+    def glups(self) -> float:
+        if self.elapsed_s <= 0:
+            return float("nan")
+        return self.nx * self.ny * max(self.steps_done, 0) / self.elapsed_s / 1e9
+
+
+class TileEngine:
+    """One tile's plan plus the bookkeeping the flag protocol needs."""
+
+    def __init__(self, field: TileField, phys: N.Phys, kmax: int, chunk_rows: int, world: int,
+                 rank: int, flags_in: torch.Tensor, vals: torch.Tensor, nflags: torch.Tensor,
+                 spin_timeout_s: float = 10.0):
+        self.field = field
+        self.phys = phys
+        self.kmax = kmax
+        self.chunk_rows = chunk_rows
+        self.world, self.rank = world, rank
+        self.flags_in, self.vals, self.nflags = flags_in, vals, nflags
+        self.spin_timeout_s = spin_timeout_s
+        dev = field.device
+        self.norm_total = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.stop = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.plan: Optional[K.Plan] = None
+        self.vals_ptrs = None
+        self.flags_ptrs = None
+
+    def build(self, peers: Dict[str, Optional[K.PeerRef]], all_vals_ptrs: List[int],
+              all_nflags_ptrs: List[int]):
+        f = self.field
+        self.plan = K.Plan(f.tile, self.phys, f.buf[0].data_ptr(), f.buf[1].data_ptr(), self.kmax,
+                           self.chunk_rows, peers=peers, flags_in_ptr=self.flags_in.data_ptr(),
+                           spin_timeout_s=self.spin_timeout_s, device=f.device)
+        self.vals_ptrs = torch.tensor(all_vals_ptrs, dtype=torch.int64, device=f.device)
+        self.flags_ptrs = torch.tensor(all_nflags_ptrs, dtype=torch.int64, device=f.device)
+        self._fault = tensor_from_ptr(self.plan.fault_ptr, (1,), torch.int32, f.device)
+
+    def launch(self, parity: int, k: int, epoch: int, norm: str):
+        self.plan.launch(parity, k, epoch, norm)
+
+    def finish(self, seq: int, norm: str, eps: float, phase: int):
+        """phase 0 = publish, 1 = combine, 2 = publish + wait + combine."""
+        lib = N.cuda()
+        dev = self.field.device
+        with torch.cuda.device(dev):
+            N.check(lib, lib.h2d_cuda_norm_finish(
+                self.plan.norm_ptr, self.vals_ptrs.data_ptr(), self.flags_ptrs.data_ptr(), self.rank,
+                self.world, seq & 0xFFFFFFFF, N.NORM[norm], float(eps), self.norm_total.data_ptr(),
+                self.stop.data_ptr(), phase, int(self.spin_timeout_s * 1e9), self.plan.fault_ptr,
+                int(torch.cuda.current_stream(dev).cuda_stream)))
+
+    def fault(self) -> int:
+        return int(self._fault.item())
+
+
+class Heat2DSolver:
+    """Single-process solver: one GPU, one tile or P x Q virtual tiles.
+
+    >>> s = Heat2DSolver(HeatConfig(nx=640, ny=512, steps=1000, k=8))
+    >>> s.initialize(); res = s.run(); u = s.gather()
+    """
+
+    def __init__(self, cfg: HeatConfig, device="cuda:0"):
+        self.cfg = cfg.validate()
+        self.device = torch.device(device)
+        if self.cfg.backend == "cpu":
+            raise ValueError("use heat2d_b200.models.cpu.CpuSolver for the cpu backend")
+        self.decomp = Decomposition(cfg.nx, cfg.ny, cfg.px, cfg.py, cfg.uneven)
+        self.phys = N.make_phys(cfg.cx_eff, cfg.cy_eff, cfg.boundary, cfg.arith)
+        self.world = self.decomp.world
+        if self.world > 1 and cfg.k > self.decomp.min_extent():
+            raise ValueError(f"k = {cfg.k} exceeds the smallest tile extent {self.decomp.min_extent()}")
+        self.parity = 0
+        self.epoch = 0
+        self.norm_seq = 0
+        self.steps_done = cfg.start_step
+        self.fields: List[TileField] = []
+        self.engines: List[TileEngine] = []
+        self._resident_buf = None
+        self._build()
+
+    # ------------------------------------------------------------------ build
+    def _build(self):
+        cfg, dev = self.cfg, self.device
+        for spec in self.decomp.tiles:
+            self.fields.append(TileField(spec, cfg.nx, cfg.ny, cfg.halo, dev))
+        if cfg.backend in ("plain", "resident"):
+            if self.world != 1:
+                raise ValueError(f"backend {cfg.backend!r} needs px = py = 1 in a single process")
+            return
+        w = self.world
+        for r, f in enumerate(self.fields):
+            flags_in = torch.zeros(64, dtype=torch.int32, device=dev)
+            vals = torch.zeros(2 * w, dtype=torch.float32, device=dev)
+            nflags = torch.zeros(2 * w, dtype=torch.int32, device=dev)
+            self.engines.append(TileEngine(f, self.phys, max(cfg.k, 1), cfg.chunk_rows, w, r, flags_in,
+                                           vals, nflags, cfg.spin_timeout_s))
+        all_vals = [e.vals.data_ptr() for e in self.engines]
+        all_nfl = [e.nflags.data_ptr() for e in self.engines]
+        for r, e in enumerate(self.engines):
+            peers: Dict[str, Optional[K.PeerRef]] = {}
+            for d, nb in self.decomp.tile(r).neighbours.items():
+                if nb is None:
+                    peers[d] = None
+                    continue
+                nf = self.fields[nb]
+                # I publish my epoch into the slot of the neighbour's flags_in that
+                # is indexed by the direction I am in as seen from there.
+                slot = N.DIRS.index(OPPOSITE[d])
+                peers[d] = K.PeerRef(nf.buf[0].data_ptr(), nf.buf[1].data_ptr(),
+                                     self.engines[nb].flags_in.data_ptr() + 4 * slot,
+                                     nf.tile.x0, nf.tile.y0, nf.tile.halo_r, nf.tile.halo_c, nf.tile.pitch)
+            e.build(peers if w > 1 else {}, all_vals, all_nfl)
+
+    # ------------------------------------------------------------- initialise
+    def initialize(self, mode: Optional[str] = None):
+        """Initial condition, evaluated tile-locally including the ghost margins
+        (``grad1612_mpi_heat.c:163-168``: every rank fills its own tile, no scatter)."""
+        mode = mode or self.cfg.init
+        for f in self.fields:
+            f.buf[1].zero_()
+            K.init_field(f.buf[0], f.tile, mode, True)
+        self.parity = 0
+        self.steps_done = self.cfg.start_step
+        return self
+
+    def load(self, grid, parity: int = 0):
+        """Scatter a full nx x ny grid (host or device tensor / ndarray) to the tiles."""
+        if isinstance(grid, np.ndarray):
+            grid = torch.from_numpy(grid)
+        assert tuple(grid.shape) == (self.cfg.nx, self.cfg.ny), "grid shape mismatch"
+        for f in self.fields:
+            f.buf[1 - parity].zero_()
+            f.load_from_global(grid, parity)
+        self.parity = parity
+        return self
+
+    # -------------------------------------------------------------------- run
+    def schedule(self, steps: Optional[int] = None) -> List[Launch]:
+        cfg = self.cfg
+        steps = cfg.steps if steps is None else steps
+        k = 1 if cfg.backend == "plain" else cfg.k
+        return make_schedule(steps, k, cfg.conv, cfg.interval, cfg.conv_mode, self.steps_done)
+
+    def _launch_all(self, L: Launch, norm: str):
+        cfg = self.cfg
+        if cfg.backend == "plain":
+            f = self.fields[0]
+            K.step_plain(f.buf[self.parity], f.buf[1 - self.parity], f.tile, self.phys)
+            return
+        self.epoch += 1
+        for e in self.engines:
+            e.launch(self.parity, L.k, self.epoch, norm)
+
+    def _norm_value(self, norm: str) -> float:
+        """Finish the cross-tile reduction and read the decision back (one sync)."""
+        cfg = self.cfg
+        if cfg.backend == "plain":
+            f = self.fields[0]
+            v = K.norm_diff(f.buf[1 - self.parity], f.buf[self.parity], f.tile, norm)
+            return float(v.item())
+        self.norm_seq += 1
+        if self.world == 1:
+            self.engines[0].finish(self.norm_seq, norm, cfg.eps, 2)
+        else:
+            for e in self.engines:
+                e.finish(self.norm_seq, norm, cfg.eps, 0)
+            for e in self.engines:
+                e.finish(self.norm_seq, norm, cfg.eps, 1)
+        return float(self.engines[0].norm_total.item())
+
+    def run(self, steps: Optional[int] = None) -> RunResult:
+        cfg = self.cfg
+        steps = cfg.steps if steps is None else steps
+        if cfg.backend == "resident":
+            return self._run_resident(steps)
+        sched = self.schedule(steps)
+        norm = cfg.norm if cfg.conv else "none"
+        ev0 = torch.cuda.Event(enable_timing=True)
+        ev1 = torch.cuda.Event(enable_timing=True)
+        converged, last_norm, checks, launches = False, float("nan"), 0, 0
+        iterations = None
+        with torch.cuda.device(self.device):
+            ev0.record()
+            for L in sched:
+                check = L.check and cfg.conv
+                self._launch_all(L, norm if check else "none")
+                launches += 1 if cfg.backend == "plain" else len(self.engines)
+                if check:
+                    last_norm = self._norm_value(norm)
+                    checks += 1
+                    if last_norm < cfg.eps:
+                        converged = True
+                        if cfg.conv_mode == "exact":
+                            # break before the flip: the pre-step field is the result
+                            iterations = L.first_step
+                        else:
+                            self.parity ^= 1
+                            self.steps_done += L.k
+                            iterations = self.steps_done
+                        break
+                self.parity ^= 1
+                self.steps_done += L.k
+            ev1.record()
+            ev1.synchronize()
+        self._check_faults()
+        if iterations is None:
+            iterations = self.steps_done
+        return RunResult(self.steps_done, iterations, converged, last_norm,
+                         ev0.elapsed_time(ev1) / 1e3, launches, checks, cfg.nx, cfg.ny)
+
+    def _run_resident(self, steps: int) -> RunResult:
+        cfg = self.cfg
+        if cfg.conv:
+            raise ValueError("the resident backend has no convergence test; use backend='fused'")
+        f = self.fields[0]
+        ev0 = torch.cuda.Event(enable_timing=True)
+        ev1 = torch.cuda.Event(enable_timing=True)
+        with torch.cuda.device(self.device):
+            ev0.record()
+            K.resident_run(f.owned(self.parity), f.owned(1 - self.parity), steps, self.phys)
+            ev1.record()
+            ev1.synchronize()
+        self.parity ^= 1
+        self.steps_done += steps
+        return RunResult(self.steps_done, self.steps_done, False, float("nan"),
+                         ev0.elapsed_time(ev1) / 1e3, 1, 0, cfg.nx, cfg.ny)
+
+    def _check_faults(self):
+        for e in self.engines:
+            code = e.fault()
+            if code:
+                raise RuntimeError(
+                    f"rank {e.rank}: flag wait timed out (code {code}: "
+                    f"{'direction ' + N.DIRS[code - 1] if code < 100 else 'norm slot of rank ' + str(code - 100)})")
+
+    # ----------------------------------------------------------------- output
+    def gather(self, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Assemble the current field as one nx x ny host tensor (pinned if given)."""
+        cfg = self.cfg
+        if out is None:
+            out = torch.empty((cfg.nx, cfg.ny), dtype=torch.float32)
+        for f in self.fields:
+            t = f.tile
+            out[t.x0:t.x0 + t.rows, t.y0:t.y0 + t.cols].copy_(f.owned(self.parity), non_blocking=True)
+        torch.cuda.synchronize(self.device)
+        return out
+
+    def owned_views(self) -> List[torch.Tensor]:
+        return [f.owned(self.parity) for f in self.fields]
+
+    @property
+    def kernel_launches(self) -> int:
+        return sum(e.plan.launch_count for e in self.engines)
+
+    def close(self):
+        for e in self.engines:
+            if e.plan is not None:
+                e.plan.close()
+        self.engines = []

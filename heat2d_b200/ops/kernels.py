@@ -1,0 +1,241 @@
+"""Thin Python wrappers over the C ABI (tensors in, raw pointers out).
+
+Every CUDA op launches one of *our* kernels on the current torch stream; there
+is no PyTorch fallback — a missing ``libheat2d_cuda.so`` raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import numpy as np
+import torch
+
+from .. import _native as N
+
+# ------------------------------------------------------------------- helpers
+
+
+def _stream_ptr(device=None) -> int:
+    return int(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _chk_dev(t: torch.Tensor, name: str):
+    if not t.is_cuda:
+        raise ValueError(f"{name} must be a CUDA tensor")
+    if t.dtype != torch.float32:
+        raise ValueError(f"{name} must be float32")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous (padded array)")
+
+
+def _padded_ok(t: torch.Tensor, tile: N.Tile, name: str):
+    need = (tile.rows + 2 * tile.halo_r, tile.pitch)
+    if tuple(t.shape) != need:
+        raise ValueError(f"{name}: expected padded shape {need}, got {tuple(t.shape)}")
+
+
+# ---------------------------------------------------------------------- CPU
+
+
+def cpu_init(base: np.ndarray, tile: N.Tile, mode: str = "exact", with_margins: bool = True):
+    """Fill a padded host array with the initial condition (inidat, mpi_heat2Dn.c:242-248)."""
+    assert base.dtype == np.float32 and base.flags.c_contiguous
+    lib = N.cpu()
+    N.check(lib, lib.h2d_cpu_init(base.ctypes.data, C.byref(tile), N.INIT[mode], int(with_margins)))
+    return base
+
+
+def cpu_initial_grid(nx: int, ny: int, mode: str = "exact") -> np.ndarray:
+    u = np.zeros((nx, ny), dtype=np.float32)
+    cpu_init(u, N.make_tile(nx, ny), mode, False)
+    return u
+
+
+def cpu_run(u: np.ndarray, steps: int, phys: N.Phys, norm: str = "none", interval: int = 20,
+            eps: float = 0.1, threads: int = 1):
+    """Oracle: advance the dense grid `u` in place.  Returns (steps_done, last_norm)."""
+    assert u.dtype == np.float32 and u.flags.c_contiguous and u.ndim == 2
+    lib = N.cpu()
+    last = C.c_double(float("nan"))
+    done = lib.h2d_cpu_run(u.ctypes.data, u.shape[0], u.shape[1], int(steps), C.byref(phys),
+                           N.NORM[norm], int(interval), float(eps), int(threads), C.byref(last))
+    N.check(lib, done)
+    return int(done), float(last.value)
+
+
+def cpu_step_tile(src: np.ndarray, dst: np.ndarray, tile: N.Tile, phys: N.Phys):
+    lib = N.cpu()
+    N.check(lib, lib.h2d_cpu_step_tile(src.ctypes.data, dst.ctypes.data, C.byref(tile), C.byref(phys)))
+
+
+# --------------------------------------------------------------------- CUDA
+
+
+def device_info(device: int = 0) -> str:
+    lib = N.cuda()
+    buf = C.create_string_buffer(1024)
+    N.check(lib, lib.h2d_cuda_device_info(device, buf, 1024))
+    return buf.value.decode()
+
+
+def init_field(base: torch.Tensor, tile: N.Tile, mode: str = "exact", with_margins: bool = True):
+    """K1: initial condition on the device, margins included (so no start-up
+    halo exchange is needed: every rank can evaluate the formula in its ghosts)."""
+    _chk_dev(base, "base")
+    _padded_ok(base, tile, "base")
+    lib = N.cuda()
+    with torch.cuda.device(base.device):
+        N.check(lib, lib.h2d_cuda_init(base.data_ptr(), C.byref(tile), N.INIT[mode], int(with_margins),
+                                       _stream_ptr(base.device)))
+    return base
+
+
+def step_plain(src: torch.Tensor, dst: torch.Tensor, tile: N.Tile, phys: N.Phys):
+    """K2/K3: one time step with the plain (k = 1, no TMA) kernel."""
+    _chk_dev(src, "src"); _chk_dev(dst, "dst")
+    _padded_ok(src, tile, "src"); _padded_ok(dst, tile, "dst")
+    lib = N.cuda()
+    with torch.cuda.device(src.device):
+        N.check(lib, lib.h2d_cuda_step_k1(src.data_ptr(), dst.data_ptr(), C.byref(tile), C.byref(phys),
+                                          _stream_ptr(src.device)))
+
+
+def norm_diff(a: torch.Tensor, b: torch.Tensor, tile: N.Tile, norm: str,
+              scratch: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None):
+    """norm of (a - b) over the owned cells -> 1-element device tensor."""
+    _chk_dev(a, "a"); _chk_dev(b, "b")
+    lib = N.cuda()
+    need = lib.h2d_norm_scratch_bytes(C.byref(tile))
+    if scratch is None:
+        scratch = torch.zeros((need + 3) // 4, dtype=torch.int32, device=a.device)
+    if out is None:
+        out = torch.zeros(1, dtype=torch.float32, device=a.device)
+    with torch.cuda.device(a.device):
+        N.check(lib, lib.h2d_cuda_norm_diff(a.data_ptr(), b.data_ptr(), C.byref(tile), N.NORM[norm],
+                                            scratch.data_ptr(), out.data_ptr(), _stream_ptr(a.device)))
+    return out
+
+
+def resident_fits(nx: int, ny: int) -> int:
+    return int(N.cuda().h2d_resident_fits(nx, ny))
+
+
+def resident_run(src: torch.Tensor, dst: torch.Tensor, steps: int, phys: N.Phys):
+    """Whole run in one cluster launch (dense nx x ny tensors, any row pitch)."""
+    assert src.is_cuda and dst.is_cuda and src.dtype == torch.float32 and dst.dtype == torch.float32
+    assert src.dim() == 2 and src.shape == dst.shape and src.stride(1) == 1 and dst.stride(1) == 1
+    assert src.stride(0) == dst.stride(0)
+    lib = N.cuda()
+    with torch.cuda.device(src.device):
+        N.check(lib, lib.h2d_resident_run(src.data_ptr(), dst.data_ptr(), src.shape[0], src.shape[1],
+                                          src.stride(0), int(steps), C.byref(phys),
+                                          _stream_ptr(src.device)))
+
+
+def pack_edge(base: torch.Tensor, tile: N.Tile, direction: str, w: int, out: torch.Tensor):
+    lib = N.cuda()
+    with torch.cuda.device(base.device):
+        N.check(lib, lib.h2d_cuda_pack_edge(base.data_ptr(), C.byref(tile), N.DIRS.index(direction), w,
+                                            out.data_ptr(), _stream_ptr(base.device)))
+    return out
+
+
+def unpack_ghost(base: torch.Tensor, tile: N.Tile, direction: str, w: int, inp: torch.Tensor):
+    lib = N.cuda()
+    with torch.cuda.device(base.device):
+        N.check(lib, lib.h2d_cuda_unpack_ghost(base.data_ptr(), C.byref(tile), N.DIRS.index(direction), w,
+                                               inp.data_ptr(), _stream_ptr(base.device)))
+
+
+class PeerRef:
+    """What a plan needs to know about one neighbour (all raw device addresses)."""
+
+    def __init__(self, buf0: int, buf1: int, flag: int, x0: int, y0: int, halo_r: int, halo_c: int,
+                 pitch: int):
+        self.buf0, self.buf1, self.flag = int(buf0), int(buf1), int(flag)
+        self.x0, self.y0, self.halo_r, self.halo_c, self.pitch = x0, y0, halo_r, halo_c, int(pitch)
+
+
+class Plan:
+    """The temporal-blocked, TMA-fed, halo-fusing stencil for one tile (K4-K7)."""
+
+    def __init__(self, tile: N.Tile, phys: N.Phys, buf0_ptr: int, buf1_ptr: int, kmax: int,
+                 chunk_rows: int = 0, peers: Optional[dict] = None, flags_in_ptr: int = 0,
+                 scratch_ptr: int = 0, spin_timeout_s: float = 10.0, device=None):
+        self._lib = N.cuda()
+        self.tile, self.phys, self.kmax = tile, phys, kmax
+        self.device = device
+        d = N.PlanDesc()
+        d.tile = tile
+        d.phys = phys
+        d.buf[0] = buf0_ptr
+        d.buf[1] = buf1_ptr
+        d.kmax = kmax
+        d.chunk_rows = chunk_rows
+        if peers:
+            for name, p in peers.items():
+                if p is None:
+                    continue
+                e = d.peer[N.DIRS.index(name)]
+                e.buf[0] = p.buf0
+                e.buf[1] = p.buf1
+                e.flag = p.flag
+                e.x0, e.y0, e.halo_r, e.halo_c, e.pitch = p.x0, p.y0, p.halo_r, p.halo_c, p.pitch
+        d.flags_in = flags_in_ptr or None
+        d.scratch = scratch_ptr or None
+        d.spin_timeout_ns = int(spin_timeout_s * 1e9)
+        self._desc = d
+        with torch.cuda.device(device):
+            h = self._lib.h2d_plan_create(C.byref(d))
+        if not h:
+            raise N.NativeError(-1, N.last_error(self._lib))
+        self._h = h
+
+    @staticmethod
+    def scratch_bytes(tile: N.Tile, kmax: int, chunk_rows: int = 0) -> int:
+        return int(N.cuda().h2d_plan_scratch_bytes(C.byref(tile), kmax, chunk_rows))
+
+    def launch(self, src_parity: int, k: int, epoch: int, norm: str = "none"):
+        with torch.cuda.device(self.device):
+            N.check(self._lib, self._lib.h2d_plan_launch(self._h, src_parity, k, epoch & 0xFFFFFFFF,
+                                                         N.NORM[norm], _stream_ptr(self.device)))
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.h2d_plan_launch_count(self._h))
+
+    @property
+    def norm_ptr(self) -> int:
+        return int(self._lib.h2d_plan_norm_ptr(self._h))
+
+    @property
+    def fault_ptr(self) -> int:
+        return int(self._lib.h2d_plan_fault_ptr(self._h))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.h2d_plan_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class DevWord:
+    """A torch view of a 4-byte device word at a raw address (read-back helper)."""
+
+    def __init__(self, ptr: int, dtype, device):
+        self.ptr = ptr
+        self.dtype = dtype
+        self.device = device
+        self.__cuda_array_interface__ = {
+            "shape": (1,), "typestr": "<f4" if dtype == torch.float32 else "<i4",
+            "data": (ptr, False), "version": 2, "strides": None,
+        }
+
+    def tensor(self) -> torch.Tensor:
+        return torch.as_tensor(self, device=self.device)

@@ -1,0 +1,212 @@
+"""Every sm_100a kernel against the CPU oracle (bit-exact: the oracle uses the
+same operation order, SURVEY 4 "Kernel")."""
+import numpy as np
+import pytest
+import torch
+
+from heat2d_b200 import _native as N
+from heat2d_b200.config import HeatConfig
+from heat2d_b200.models.heat import Heat2DSolver, TileField, padded_geometry
+from heat2d_b200.ops import kernels as K
+from heat2d_b200.parallel.decomp import Decomposition
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+
+
+def oracle(nx, ny, steps, boundary="fixed", arith="fp32", init="exact", u0=None):
+    u = K.cpu_initial_grid(nx, ny, init) if u0 is None else u0.copy()
+    K.cpu_run(u, steps, N.make_phys(0.1, 0.1, boundary, arith))
+    return u
+
+
+def rand_grid(nx, ny, seed=0):
+    return (np.random.default_rng(seed).random((nx, ny), dtype=np.float32) * 1e4).astype(np.float32)
+
+
+def test_library_loaded(native_cuda):
+    assert b"heat2d" in native_cuda.h2d_version()
+    assert "B200" in K.device_info(0) or "NVIDIA" in K.device_info(0)
+
+
+@pytest.mark.parametrize("mode", ["exact", "ref-int32", "ref-uint32", "zero"])
+@pytest.mark.parametrize("shape", [(10, 10), (640, 640), (700, 1000)])
+def test_init_kernel(mode, shape):
+    nx, ny = shape
+    d = Decomposition(nx, ny, 1, 1)
+    f = TileField(d.tile(0), nx, ny, 8, DEV)
+    f.buf[0].fill_(-3.0)
+    K.init_field(f.buf[0], f.tile, mode, True)
+    want = np.zeros(tuple(f.buf[0].shape), dtype=np.float32)
+    K.cpu_init(want, f.tile, mode, True)
+    got = f.buf[0].cpu().numpy()
+    t = f.tile
+    w = t.cols + 2 * t.halo_c
+    assert np.array_equal(got[:, :w], want[:, :w])
+
+
+def test_init_kernel_tile_margins_hold_neighbour_values():
+    nx, ny = 96, 160
+    d = Decomposition(nx, ny, 2, 2)
+    full = K.cpu_initial_grid(nx, ny, "exact")
+    for spec in d.tiles:
+        f = TileField(spec, nx, ny, 8, DEV)
+        K.init_field(f.buf[0], f.tile, "exact", True)
+        gx0, gx1, gy0, gy1, r0, c0 = f.padded_window()
+        got = f.buf[0].cpu().numpy()[r0:r0 + gx1 - gx0, c0:c0 + gy1 - gy0]
+        assert np.array_equal(got, full[gx0:gx1, gy0:gy1])
+
+
+@pytest.mark.parametrize("arith", ["fp32", "strict", "strict-fma"])
+@pytest.mark.parametrize("boundary", ["fixed", "ghost-ring"])
+@pytest.mark.parametrize("shape", [(10, 10), (80, 64), (257, 391)])
+def test_plain_kernel_bit_exact(arith, boundary, shape):
+    nx, ny = shape
+    u0 = rand_grid(nx, ny, 5)
+    cfg = HeatConfig(nx=nx, ny=ny, steps=7, backend="plain", arith=arith, boundary=boundary, k=1)
+    s = Heat2DSolver(cfg, DEV).load(u0)
+    res = s.run()
+    assert res.steps_done == 7
+    assert np.array_equal(s.gather().numpy(), oracle(nx, ny, 7, boundary, arith, u0=u0))
+
+
+@pytest.mark.parametrize("k", [1, 2, 3, 4, 5, 6, 7, 8])
+@pytest.mark.parametrize("boundary", ["fixed", "ghost-ring"])
+def test_tk_kernel_every_k_bit_exact(k, boundary):
+    nx, ny = 150, 333      # several strips, partial last strip, odd sizes
+    u0 = rand_grid(nx, ny, k)
+    cfg = HeatConfig(nx=nx, ny=ny, steps=2 * k + 1, k=k, boundary=boundary, chunk_rows=32)
+    s = Heat2DSolver(cfg, DEV).load(u0)
+    res = s.run()
+    assert res.steps_done == 2 * k + 1
+    assert np.array_equal(s.gather().numpy(), oracle(nx, ny, 2 * k + 1, boundary, "fp32", u0=u0))
+
+
+@pytest.mark.parametrize("arith", ["strict", "strict-fma"])
+def test_tk_kernel_strict_modes(arith):
+    nx, ny = 96, 200
+    u0 = rand_grid(nx, ny, 11)
+    cfg = HeatConfig(nx=nx, ny=ny, steps=24, k=8, arith=arith, chunk_rows=32)
+    s = Heat2DSolver(cfg, DEV).load(u0)
+    s.run()
+    assert np.array_equal(s.gather().numpy(), oracle(nx, ny, 24, "fixed", arith, u0=u0))
+
+
+@pytest.mark.parametrize("shape", [(10, 10), (80, 64), (640, 512), (1030, 2050)])
+def test_tk_kernel_reference_sizes(shape):
+    nx, ny = shape
+    cfg = HeatConfig(nx=nx, ny=ny, steps=100, k=8, init="exact")
+    s = Heat2DSolver(cfg, DEV).initialize()
+    s.run()
+    assert np.array_equal(s.gather().numpy(), oracle(nx, ny, 100))
+
+
+def test_temporal_blocking_equals_single_steps():
+    nx, ny = 300, 500
+    u0 = rand_grid(nx, ny, 2)
+    outs = []
+    for k in (1, 4, 8):
+        s = Heat2DSolver(HeatConfig(nx=nx, ny=ny, steps=40, k=k), DEV).load(u0)
+        s.run()
+        outs.append(s.gather().numpy())
+    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
+
+
+@pytest.mark.parametrize("px,py", [(2, 2), (2, 4), (3, 1), (1, 3), (4, 2)])
+@pytest.mark.parametrize("boundary", ["fixed", "ghost-ring"])
+def test_virtual_tiles_equal_single_tile(px, py, boundary):
+    # P x Q result == 1 x 1 result bit for bit: the peer-store / flag
+    # code path of the multi-GPU kernel, pointed at local buffers.
+    nx, ny = 203, 317      # uneven splits
+    u0 = rand_grid(nx, ny, 9)
+    cfg = HeatConfig(nx=nx, ny=ny, steps=41, k=8, px=px, py=py, boundary=boundary, chunk_rows=16)
+    s = Heat2DSolver(cfg, DEV).load(u0)
+    res = s.run()
+    assert res.steps_done == 41
+    assert np.array_equal(s.gather().numpy(), oracle(nx, ny, 41, boundary, "fp32", u0=u0))
+
+
+def test_virtual_tiles_init_needs_no_exchange():
+    cfg = HeatConfig(nx=256, ny=384, steps=32, k=8, px=2, py=2)
+    s = Heat2DSolver(cfg, DEV).initialize()
+    s.run()
+    assert np.array_equal(s.gather().numpy(), oracle(256, 384, 32))
+
+
+@pytest.mark.parametrize("norm", ["l2sq", "linf"])
+def test_norm_diff_kernel(norm):
+    nx, ny = 123, 457
+    d = Decomposition(nx, ny, 1, 1)
+    f = TileField(d.tile(0), nx, ny, 8, DEV)
+    a, b = rand_grid(nx, ny, 1), rand_grid(nx, ny, 2)
+    f.owned(0).copy_(torch.from_numpy(a))
+    f.owned(1).copy_(torch.from_numpy(b))
+    got = float(K.norm_diff(f.buf[0], f.buf[1], f.tile, norm).item())
+    d64 = a.astype(np.float64) - b.astype(np.float64)
+    want = float((d64 ** 2).sum()) if norm == "l2sq" else float(np.abs(d64).max())
+    assert got == pytest.approx(want, rel=1e-5)
+    # second call on the same scratch-free path gives the same bits (deterministic order)
+    assert float(K.norm_diff(f.buf[0], f.buf[1], f.tile, norm).item()) == got
+
+
+@pytest.mark.parametrize("conv_mode", ["exact", "fused-k"])
+@pytest.mark.parametrize("px,py", [(1, 1), (2, 2)])
+def test_convergence_stops_like_the_oracle(conv_mode, px, py):
+    nx, ny = 24, 24
+    u0 = K.cpu_initial_grid(nx, ny, "exact")
+    phys = N.make_phys(0.1, 0.1, "ghost-ring", "fp32")
+    ref = u0.copy()
+    done, last = K.cpu_run(ref, 100000, phys, norm="l2sq", interval=20, eps=0.1)
+    assert 0 < done < 100000
+    cfg = HeatConfig(nx=nx, ny=ny, steps=100000, k=8, px=px, py=py, boundary="ghost-ring", conv=True,
+                     interval=20, eps=0.1, conv_mode=conv_mode)
+    s = Heat2DSolver(cfg, DEV).initialize()
+    res = s.run()
+    assert res.converged
+    assert res.last_norm == pytest.approx(last, rel=1e-3)
+    if conv_mode == "exact":
+        assert res.iterations == done and res.steps_done == done
+        assert np.array_equal(s.gather().numpy(), ref)
+    else:
+        assert res.steps_done == done + 1
+        nxt = ref.copy()
+        K.cpu_run(nxt, 1, phys)
+        assert np.array_equal(s.gather().numpy(), nxt)
+
+
+def test_fused_norm_matches_standalone():
+    nx, ny = 500, 700
+    u0 = rand_grid(nx, ny, 21)
+    cfg = HeatConfig(nx=nx, ny=ny, steps=1, k=1, conv=True, interval=1, eps=0.0, norm="linf")
+    s = Heat2DSolver(cfg, DEV).load(u0)
+    res = s.run()
+    one = oracle(nx, ny, 1, u0=u0)
+    assert res.last_norm == pytest.approx(float(np.abs(one.astype(np.float64) - u0).max()), rel=1e-6)
+
+
+@pytest.mark.parametrize("shape", [(10, 10), (80, 64), (320, 256), (640, 512)])
+@pytest.mark.parametrize("boundary", ["fixed", "ghost-ring"])
+def test_resident_cluster_kernel(shape, boundary):
+    nx, ny = shape
+    assert K.resident_fits(nx, ny) >= 1
+    cfg = HeatConfig(nx=nx, ny=ny, steps=100, backend="resident", boundary=boundary)
+    s = Heat2DSolver(cfg, DEV).initialize()
+    res = s.run()
+    assert res.launches == 1
+    assert np.array_equal(s.gather().numpy(), oracle(nx, ny, 100, boundary))
+
+
+def test_resident_rejects_big_grid():
+    assert K.resident_fits(4096, 4096) == 0
+
+
+def test_bad_arguments_raise():
+    d = Decomposition(64, 64, 1, 1)
+    f = TileField(d.tile(0), 64, 64, 8, DEV)
+    with pytest.raises(N.NativeError):
+        K.Plan(f.tile, N.make_phys(), f.buf[0].data_ptr(), f.buf[1].data_ptr(), kmax=9)
+    p = K.Plan(f.tile, N.make_phys(), f.buf[0].data_ptr(), f.buf[1].data_ptr(), kmax=4)
+    with pytest.raises(N.NativeError):
+        p.launch(0, 5, 1)
+    p.close()
