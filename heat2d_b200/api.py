@@ -1,0 +1,52 @@
+"""The call a user makes: build the right solver for the configuration and the
+launch environment, run it, return the result and the final field.
+
+    from heat2d_b200 import HeatConfig, solve
+    res, field = solve(HeatConfig(nx=2560, ny=2048, steps=1000))
+
+Under ``torchrun`` (WORLD_SIZE > 1) the same call runs one tile per GPU.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from .config import HeatConfig
+
+
+def make_solver(cfg: HeatConfig, device=None):
+    """Pick the solver class for `cfg.backend` and the current process group."""
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    if cfg.backend == "cpu":
+        from .models.cpu import CpuSolver
+        return CpuSolver(cfg)
+    if cfg.backend == "nccl-halo":
+        from .parallel.dist import HaloExchangeSolver
+        return HaloExchangeSolver(cfg, device)
+    if world > 1 and cfg.backend == "fused":
+        from .parallel.dist import DistributedHeat2DSolver
+        return DistributedHeat2DSolver(cfg, device)
+    from .models.heat import Heat2DSolver
+    if cfg.backend == "single":
+        cfg = cfg.replace(backend="fused", px=1, py=1)
+    return Heat2DSolver(cfg, device or "cuda:0")
+
+
+def solve(cfg: HeatConfig, u0=None, device=None, gather: bool = True) -> Tuple[object, Optional[torch.Tensor]]:
+    """Initialise (or load `u0`, a full nx x ny host array), run `cfg.steps`
+    steps and return ``(RunResult, final field on the host or None)``."""
+    s = make_solver(cfg, device)
+    try:
+        if u0 is None:
+            s.initialize()
+        else:
+            s.load(u0)
+        res = s.run()
+        field = s.gather() if gather else None
+    finally:
+        close = getattr(s, "close", None)
+        if close:
+            close()
+    return res, field
