@@ -6,6 +6,7 @@
 // row/column derived datatypes :140-144, detailsGPU() cuda:24-37.
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include "device_common.cuh"
 
 namespace h2d {
@@ -161,6 +162,15 @@ norm_diff_kernel(const float* __restrict__ a, const float* __restrict__ b, Geo g
   }
 }
 
+// ---- scratch of the no-allocation norm entry point (h2d_cuda_norm_diff_static) ----
+// Lives in the library image: every GPU that loads libheat2d_cuda.so carries
+// these 64 KiB + 256 B until the process exits.  Same layout as the caller-
+// provided scratch of h2d_cuda_norm_diff: a 64-byte header whose first word is
+// the block counter, then one float per block.
+constexpr int NORM_STATIC_MAX_BLOCKS = H2D_NORM_STATIC_MAX_ROWS / NORM_ROWS_PER_BLOCK;
+constexpr size_t NORM_STATIC_BYTES = 256 + (size_t)NORM_STATIC_MAX_BLOCKS * sizeof(float);
+static __device__ __align__(256) unsigned char g_norm_static_scratch[NORM_STATIC_BYTES];
+
 // ------------------------------------------------ halo pack / unpack (baseline)
 // dir N/S: w rows x cols, row-major.  dir W/E: rows x w, row-major.
 __global__ void pack_edge_kernel(const float* __restrict__ base, Geo g, int dir, int w,
@@ -299,6 +309,63 @@ int h2d_cuda_norm_diff(const float* a, const float* b, const h2d_tile_t* t, int 
   norm_diff_kernel<<<blocks, NORM_THREADS, 0, (cudaStream_t)stream>>>(a, b, g, norm, counter,
                                                                       partials, out_dev);
   H2D_CHECK_LAUNCH("norm_diff_kernel");
+  return H2D_OK;
+}
+
+// The name `g_norm_static_scratch` is only a host-side stand-in in host code;
+// the kernel needs the array's device address, which differs per GPU.  Looked up
+// once per device (with that device current) and cached.
+static int norm_static_scratch_addr(void** out) {
+  constexpr int MAX_DEVICES = 64;
+  static std::mutex mu;
+  static void* cache[MAX_DEVICES] = {nullptr};
+  int dev = -1;
+  H2D_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= MAX_DEVICES)
+    return h2d_fail(H2D_EINVAL, "h2d_cuda_norm_diff_static: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (cache[dev] == nullptr) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, g_norm_static_scratch);
+    if (e != cudaSuccess || p == nullptr)
+      return h2d_fail(H2D_ECUDA, "h2d_cuda_norm_diff_static: cudaGetSymbolAddress failed on device %d: %s",
+                      dev, cudaGetErrorString(e));
+    cache[dev] = p;
+  }
+  *out = cache[dev];
+  return H2D_OK;
+}
+
+// norm of (a - b) without any allocation, for callers that cannot allocate
+// (their own pool owns the GPU, or they must not hit cudaMalloc's device-wide
+// synchronisation).  Same kernel and same summation order as
+// h2d_cuda_norm_diff; only the scratch differs: the fixed array above, shared by
+// every call on this GPU.  Rows beyond H2D_NORM_STATIC_MAX_ROWS are refused.
+// The first call on a device performs the address look-up (do it before any
+// stream capture); calls that may overlap on the GPU race on the shared array.
+int h2d_cuda_norm_diff_static(const float* a, const float* b, const h2d_tile_t* t, int norm,
+                              float* out_dev, void* stream) {
+  if (int rc = check_common(a, t, "h2d_cuda_norm_diff_static")) return rc;
+  if (!b || !out_dev) return h2d_fail(H2D_EINVAL, "h2d_cuda_norm_diff_static: null argument");
+  if (norm != H2D_NORM_L2SQ && norm != H2D_NORM_LINF)
+    return h2d_fail(H2D_EINVAL, "h2d_cuda_norm_diff_static: unknown norm %d", norm);
+  if (t->rows > H2D_NORM_STATIC_MAX_ROWS)
+    return h2d_fail(H2D_EINVAL,
+                    "h2d_cuda_norm_diff_static: tile has %d rows, the built-in scratch covers at most %d; "
+                    "use h2d_cuda_norm_diff with caller-provided scratch",
+                    t->rows, H2D_NORM_STATIC_MAX_ROWS);
+  void* scratch = nullptr;
+  if (int rc = norm_static_scratch_addr(&scratch)) return rc;
+  h2d_phys_t ph = {0.1, 0.1, H2D_BOUNDARY_FIXED, H2D_ARITH_FP32};
+  Geo g = make_geo(*t, ph);
+  const int blocks = (t->rows + NORM_ROWS_PER_BLOCK - 1) / NORM_ROWS_PER_BLOCK;
+  cudaStream_t s = (cudaStream_t)stream;
+  // The array keeps whatever the previous call (or an aborted one) left behind:
+  // the block counter must start at zero, the partials are fully overwritten.
+  H2D_CUDA_TRY(cudaMemsetAsync(scratch, 0, 64, s));
+  norm_diff_kernel<<<blocks, NORM_THREADS, 0, s>>>(a, b, g, norm, (unsigned*)scratch,
+                                                   (float*)((char*)scratch + 64), out_dev);
+  H2D_CHECK_LAUNCH("norm_diff_kernel (static scratch)");
   return H2D_OK;
 }
 

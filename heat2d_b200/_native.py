@@ -22,6 +22,7 @@ NORM = {"none": 0, "off": 0, "l2sq": 1, "linf": 2}
 DIRS = ("N", "S", "W", "E", "NW", "NE", "SW", "SE")
 NDIR = 8
 KMAX = 8
+NORM_STATIC_MAX_ROWS = 131072
 
 H2D_OK, H2D_EINVAL, H2D_ECUDA, H2D_EIO, H2D_ETIMEOUT, H2D_ENOMEM = 0, -1, -2, -3, -4, -5
 
@@ -137,6 +138,7 @@ def cuda():
             lib.h2d_norm_scratch_bytes.argtypes = [P(Tile)]
             lib.h2d_norm_scratch_bytes.restype = C.c_size_t
             lib.h2d_cuda_norm_diff.argtypes = [vp, vp, P(Tile), C.c_int, vp, vp, vp]
+            lib.h2d_cuda_norm_diff_static.argtypes = [vp, vp, P(Tile), C.c_int, vp, vp]
             lib.h2d_cuda_norm_finish.argtypes = [vp, vp, vp, C.c_int, C.c_int, C.c_uint32, C.c_int,
                                                  C.c_float, vp, vp, C.c_int, C.c_int64, vp, vp]
             lib.h2d_cuda_pack_edge.argtypes = [vp, P(Tile), C.c_int, C.c_int, vp, vp]

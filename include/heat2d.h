@@ -221,6 +221,30 @@ size_t h2d_norm_scratch_bytes(const h2d_tile_t* tile);
 int h2d_cuda_norm_diff(const float* a, const float* b, const h2d_tile_t* tile, int norm,
                        void* scratch, float* out_dev, void* stream);
 
+/* Same result as h2d_cuda_norm_diff, for callers that cannot provide scratch
+ * memory because they cannot allocate any: programs whose own pool already
+ * owns the whole GPU (a cudaMalloc from inside this library would fail or
+ * fight that pool), and steady-state loops that must not pay the device-wide
+ * synchronisation hidden in cudaMalloc / cudaFree.  The scratch is a fixed
+ * array inside the library image instead: 64 KiB + 256 B per GPU that loads
+ * the library, held until the process exits.
+ *  - Limit: tile->rows <= H2D_NORM_STATIC_MAX_ROWS (any number of columns);
+ *    larger tiles are rejected with H2D_EINVAL and a message.
+ *  - Allocates nothing: no cudaMalloc / cudaFree, no allocating library call.
+ *    The caller still passes the inputs (a, b) and the output (out_dev).
+ *  - The first call on each device looks up the array's device address
+ *    (cudaGetSymbolAddress, with that device current) and caches it; make that
+ *    first call before starting any stream capture.
+ *  - All calls on one GPU share the one array: each call clears the words that
+ *    must start at zero on `stream` before its kernel, but two calls that can
+ *    overlap on the GPU (different streams, no ordering) race and give wrong
+ *    sums.  Serialise them, or use h2d_cuda_norm_diff with separate scratch.
+ * No counterpart in the reference (its only reduction runs on the CPU,
+ * grad1612_mpi_heat.c:264-267). */
+#define H2D_NORM_STATIC_MAX_ROWS 131072
+int h2d_cuda_norm_diff_static(const float* a, const float* b, const h2d_tile_t* tile, int norm,
+                              float* out_dev, void* stream);
+
 /* ---- cross-GPU finish of the convergence value ---------------------------- */
 /* Writes `*local_val` into slot `rank` of every peer's value table (peer
  * pointers in vals[r], one table of 2*world floats per rank: [parity][rank]),
