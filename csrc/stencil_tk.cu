@@ -19,7 +19,7 @@
 //          H = roundup4(K) columns on each side are the overlap whose results
 //          go stale as the K levels advance, the middle 128-2H are stored;
 //   chunk  R output rows; the warp streams R + 2K input rows top to bottom.
-// Each warp runs its own 4-stage TMA ring (no block-wide barrier in the loop).
+// Each warp runs its own 4-stage TMA ring of 6-row boxes (no block-wide barrier in the loop).
 // Per input row the K levels advance by one row each; level t keeps two rows
 // (up, centre) in registers, so the state is 2*4*K floats per lane.
 #include <cuda.h>
@@ -32,7 +32,7 @@
 namespace h2d {
 
 constexpr int TK_W = 128;      // floats per strip row
-constexpr int TK_BR = 4;       // rows per TMA box
+constexpr int TK_BR = 6;       // rows per TMA box (a multiple of the 3-row register rotation)
 constexpr int TK_STAGES = 4;   // boxes in flight per warp
 constexpr int TK_WARPS = 4;    // warps (tasks) per CTA
 constexpr int TK_STAGE_BYTES = TK_BR * TK_W * 4;
@@ -192,9 +192,12 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
     for (int b = 0; b < pre; ++b) issue(b);
   }
 
-  float4 st[K][2];
+  // Three row slots per level, rotating roles (up, centre, incoming) with period
+  // 3: every producer writes straight into the slot its consumer will read, so a
+  // loop body unrolled over 3 rows needs no register-to-register moves.
+  float4 st[K][3];
 #pragma unroll
-  for (int t = 0; t < K; ++t) st[t][0] = st[t][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int t = 0; t < K; ++t) st[t][0] = st[t][1] = st[t][2] = make_float4(0.f, 0.f, 0.f, 0.f);
 
   float acc = 0.f;
   // Level-K output of iteration i is tile-local row  row0 - K + i;  `ro` counts
@@ -202,15 +205,17 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
   int ro = -2 * K;
   float* q = a.dst + (int64_t)(g.halo_r + r_lo - 2 * K) * g.pitch + g.halo_c + j0;
 
-  // One input row: advance all K levels.  P = which of the two state slots
-  // holds the "up" row this iteration (alternates every row).
-  auto row_step = [&](float4 down, auto Ptag) {
-    constexpr int P = decltype(Ptag)::value;
+  // One input row (already in st[0][(PH+2)%3]): advance all K levels.
+  auto row_step = [&](auto Ptag) {
+    constexpr int PH = decltype(Ptag)::value;
+    constexpr int iu = PH, ic = (PH + 1) % 3, id = (PH + 2) % 3;
+    float4 fin;
     float4 cprev = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int t = 0; t < K; ++t) {
-      const float4 up = st[t][P];
-      const float4 c = st[t][P ^ 1];
+      const float4 up = st[t][iu];
+      const float4 c = st[t][ic];
+      const float4 down = st[t][id];
       const float L = __shfl_up_sync(0xffffffffu, c.w, 1);
       const float Rn = __shfl_down_sync(0xffffffffu, c.x, 1);
       float4 o = point4<ARITH>(up, c, down, L, Rn, g);
@@ -222,26 +227,29 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
         o.z = (ract && act[2]) ? o.z : c.z;
         o.w = (ract && act[3]) ? o.w : c.w;
       }
-      st[t][P] = down;
-      if (EXTRAS && t == K - 1) cprev = c;
-      down = o;
+      if (t + 1 < K) {
+        st[t + 1][id] = o;
+      } else {
+        fin = o;
+        if (EXTRAS) cprev = c;
+      }
     }
     if ((unsigned)ro < (unsigned)n_out) {
       if (st_full) {
-        *reinterpret_cast<float4*>(q) = down;
+        *reinterpret_cast<float4*>(q) = fin;
       } else if (st_part) {
-        if (smask & 1) q[0] = down.x;
-        if (smask & 2) q[1] = down.y;
-        if (smask & 4) q[2] = down.z;
-        if (smask & 8) q[3] = down.w;
+        if (smask & 1) q[0] = fin.x;
+        if (smask & 2) q[1] = fin.y;
+        if (smask & 4) q[2] = fin.z;
+        if (smask & 8) q[3] = fin.w;
       }
       if (EXTRAS && smask != 0) {
-        if (comm_edge) forward_row(a, r_lo + ro, j0, down, smask);
+        if (comm_edge) forward_row(a, r_lo + ro, j0, fin, smask);
         if (a.norm != H2D_NORM_NONE) {
-          const float d0 = (smask & 1) ? down.x - cprev.x : 0.f;
-          const float d1 = (smask & 2) ? down.y - cprev.y : 0.f;
-          const float d2 = (smask & 4) ? down.z - cprev.z : 0.f;
-          const float d3 = (smask & 8) ? down.w - cprev.w : 0.f;
+          const float d0 = (smask & 1) ? fin.x - cprev.x : 0.f;
+          const float d1 = (smask & 2) ? fin.y - cprev.y : 0.f;
+          const float d2 = (smask & 4) ? fin.z - cprev.z : 0.f;
+          const float d3 = (smask & 8) ? fin.w - cprev.w : 0.f;
           if (a.norm == H2D_NORM_L2SQ) {
             acc = fmaf(d0, d0, acc); acc = fmaf(d1, d1, acc);
             acc = fmaf(d2, d2, acc); acc = fmaf(d3, d3, acc);
@@ -261,11 +269,13 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
     mbar_wait(bars + s * 8, (uint32_t)((b / TK_STAGES) & 1));
     const uint32_t sbase = ring + s * TK_STAGE_BYTES + lane * 16;
 #pragma unroll 1
-    for (int rr = 0; rr < TK_BR; rr += 2) {
-      const float4 in0 = lds128(sbase + rr * (TK_W * 4));
-      const float4 in1 = lds128(sbase + (rr + 1) * (TK_W * 4));
-      row_step(in0, std::integral_constant<int, 0>{});
-      row_step(in1, std::integral_constant<int, 1>{});
+    for (int rr = 0; rr < TK_BR; rr += 3) {
+      st[0][2] = lds128(sbase + rr * (TK_W * 4));
+      row_step(std::integral_constant<int, 0>{});
+      st[0][0] = lds128(sbase + (rr + 1) * (TK_W * 4));
+      row_step(std::integral_constant<int, 1>{});
+      st[0][1] = lds128(sbase + (rr + 2) * (TK_W * 4));
+      row_step(std::integral_constant<int, 2>{});
     }
     // Everyone has read stage s: refill it with box b + STAGES.
     __syncwarp();
@@ -438,11 +448,13 @@ struct h2d_plan {
 static inline int round_up4(int k) { return (k + 3) & ~3; }
 
 static int choose_chunk_rows(int rows, int cols, int kmax) {
-  // Enough tasks for several waves of 148 SMs x 16 warps, but chunks long
-  // enough that the 2K-row pipeline fill stays a few per cent.
-  const int n_strips = (cols + (TK_W - 2 * round_up4(kmax)) - 1) / (TK_W - 2 * round_up4(kmax));
-  int R = 256;
-  while (R > 32 && (int64_t)(rows / R) * n_strips < 4 * 148 * 16) R >>= 1;
+  // Long chunks keep the 2K-row pipeline fill at a few per cent (R = 512, K = 8:
+  // 3 %), but there must be enough tasks for a couple of waves of
+  // 148 SMs x 12..16 resident warps.
+  const int wv = TK_W - 2 * round_up4(kmax);
+  const int n_strips = (cols + wv - 1) / wv;
+  int R = 512;
+  while (R > 32 && (int64_t)(rows / R) * n_strips < 3 * 148 * 16) R >>= 1;
   if (R < kmax) R = kmax;
   return R;
 }
