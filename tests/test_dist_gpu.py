@@ -1,0 +1,70 @@
+"""One process per GPU (needs >= 2 GPUs): the fused peer-memory halo exchange and
+the cross-GPU convergence finish against the CPU oracle, bit for bit."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _ngpu():
+    try:
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _run(nproc, spec, timeout=600):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
+           os.path.join(HERE, "_dist_gpu_worker.py"), json.dumps(spec)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
+    return json.loads(line)
+
+
+def _cases(px, py):
+    base = dict(nx=1000, ny=1400, px=px, py=py, k=8)
+    return [
+        {"name": "fused-k8", "random": True, "cfg": dict(base, steps=83, backend="fused")},
+        {"name": "fused-ring-k5", "random": True,
+         "cfg": dict(base, steps=42, backend="fused", k=5, boundary="ghost-ring")},
+        {"name": "fused-strict", "random": True, "cfg": dict(base, steps=24, backend="fused", arith="strict")},
+        {"name": "fused-conv", "cfg": dict(nx=48, ny=64, px=px, py=py, k=8, steps=100000, backend="fused",
+                                           boundary="ghost-ring", conv=True, interval=20, eps=0.1)},
+        {"name": "nccl-halo", "random": True, "cfg": dict(base, steps=9, backend="nccl-halo", k=1)},
+    ]
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("px,py", [(2, 1), (1, 2)])
+def test_two_gpus(px, py):
+    out = _run(2, {"cases": _cases(px, py)})
+    assert out["ok"], out
+
+
+@pytest.mark.skipif(_ngpu() < 4, reason="needs 4 GPUs")
+def test_four_gpus():
+    out = _run(4, {"cases": _cases(2, 2)})
+    assert out["ok"], out
+
+
+@pytest.mark.skipif(_ngpu() < 8, reason="needs 8 GPUs")
+def test_eight_gpus():
+    out = _run(8, {"cases": _cases(2, 4)})
+    assert out["ok"], out
