@@ -52,7 +52,9 @@ step_k1_kernel(const float* __restrict__ src, float* __restrict__ dst,
   const int strip = task % n_strips;
   const int rblk = task / n_strips;
   const int j0 = strip * 128 + lane * 4;
-  const bool lane_on = j0 < g.cols;
+  // Lanes up to and including the one that holds column `cols` load: that
+  // column is the east neighbour's ghost (halo_c >= 4 keeps the float4 in bounds).
+  const bool lane_on = j0 <= g.cols;
   const int r_lo = rblk * K1_RB;
   const int r_hi = min(r_lo + K1_RB, g.rows);
 
@@ -78,13 +80,13 @@ step_k1_kernel(const float* __restrict__ src, float* __restrict__ dst,
   float4 c = ld4(p);
   // Out-of-strip neighbours of the centre row.
   float eL = (lane == 0 && lane_on) ? __ldg(p - 1) : 0.f;
-  float eR = (lane == 31 && lane_on) ? __ldg(p + 4) : 0.f;
+  float eR = (lane == 31 && j0 < g.cols) ? __ldg(p + 4) : 0.f;
 
   for (int i = r_lo; i < r_hi; ++i) {
     p += g.pitch;
     const float4 dn = ld4(p);
     const float nL = (lane == 0 && lane_on) ? __ldg(p - 1) : 0.f;
-    const float nR = (lane == 31 && lane_on) ? __ldg(p + 4) : 0.f;
+    const float nR = (lane == 31 && j0 < g.cols) ? __ldg(p + 4) : 0.f;
     float L = __shfl_up_sync(0xffffffffu, c.w, 1);
     float R = __shfl_down_sync(0xffffffffu, c.x, 1);
     if (lane == 0) L = eL;

@@ -210,3 +210,22 @@ def test_bad_arguments_raise():
     with pytest.raises(N.NativeError):
         p.launch(0, 5, 1)
     p.close()
+
+
+@pytest.mark.parametrize("px,py", [(1, 2), (2, 2), (1, 3)])
+def test_plain_kernel_reads_ghosts_of_all_four_neighbours(px, py):
+    # the compute half of the NCCL-halo baseline: one step per tile from a field
+    # whose margins hold the neighbours' cells (cols not a multiple of 128 or 4)
+    nx, ny = 90, 1401
+    u0 = rand_grid(nx, ny, 33)
+    want = oracle(nx, ny, 1, "ghost-ring", "fp32", u0=u0)
+    d = Decomposition(nx, ny, px, py)
+    phys = N.make_phys(0.1, 0.1, "ghost-ring", "fp32")
+    got = np.zeros_like(u0)
+    g = torch.from_numpy(u0)
+    for spec in d.tiles:
+        f = TileField(spec, nx, ny, 8, DEV)
+        f.load_from_global(g, 0)
+        K.step_plain(f.buf[0], f.buf[1], f.tile, phys)
+        got[spec.x0:spec.x0 + spec.rows, spec.y0:spec.y0 + spec.cols] = f.owned(1).cpu().numpy()
+    assert np.array_equal(got, want)
