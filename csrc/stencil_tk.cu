@@ -146,7 +146,7 @@ __device__ __noinline__ void forward_row(const TkArgs& a, int rho, int j0, float
 // to neighbours and/or feeds the convergence norm.  Both are warp-uniform and
 // resolved at compile time so the common case (interior, no extras) carries
 // no overhead in its inner loop.
-template <int K, int ARITH, bool FROZEN, bool EXTRAS>
+template <int K, int ARITH, bool IMM, bool FROZEN, bool EXTRAS>
 __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs& a, int strip,
                                           int chunk, bool comm_edge, uint32_t ring,
                                           uint32_t bars, int lane) {
@@ -158,7 +158,11 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
   const int jbase = strip * a.wv - a.H;  // tile-local column of lane 0, element 0
   const int j0 = jbase + lane * 4;
   const int row0 = r_lo - K;             // first input row (tile-local)
-  const int n_in = n_out + 2 * K;
+  // (A "skewed" variant in which level t consumes what level t-1 produced in the
+  // previous row step — K independent levels per step instead of a K-long chain —
+  // was measured 11 % SLOWER on B200: the chain is not the limiter, see DESIGN.md.)
+  constexpr int LAG = 2 * K;  // row steps between reading a row and storing the row K below it
+  const int n_in = n_out + LAG;
   const int n_blk = (n_in + TK_BR - 1) / TK_BR;
   const int tc0 = g.halo_c + jbase;      // TMA coordinates of the first box
   const int tc1 = g.halo_r + row0;
@@ -202,10 +206,11 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
   float acc = 0.f;
   // Level-K output of iteration i is tile-local row  row0 - K + i;  `ro` counts
   // rows relative to r_lo so that "is an owned output row" is one unsigned compare.
-  int ro = -2 * K;
-  float* q = a.dst + (int64_t)(g.halo_r + r_lo - 2 * K) * g.pitch + g.halo_c + j0;
+  int ro = -LAG;
+  float* q = a.dst + (int64_t)(g.halo_r + r_lo - LAG) * g.pitch + g.halo_c + j0;
 
-  // One input row (already in st[0][(PH+2)%3]): advance all K levels.
+  // One row step: the input row is already in st[0][(PH+2)%3]; levels run
+  // 0..K-1, each writing its result straight into the next level's incoming slot.
   auto row_step = [&](auto Ptag) {
     constexpr int PH = decltype(Ptag)::value;
     constexpr int iu = PH, ic = (PH + 1) % 3, id = (PH + 2) % 3;
@@ -218,9 +223,10 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
       const float4 down = st[t][id];
       const float L = __shfl_up_sync(0xffffffffu, c.w, 1);
       const float Rn = __shfl_down_sync(0xffffffffu, c.x, 1);
-      float4 o = point4<ARITH>(up, c, down, L, Rn, g);
+      float4 o = point4<ARITH, IMM>(up, c, down, L, Rn, g);
       if (FROZEN) {
-        const int gx = g.x0 + r_lo + ro + (K - 1 - t);  // row of this level's output
+        // tile-local row of this level's output
+        const int gx = g.x0 + r_lo + ro + (K - 1 - t);
         const bool ract = gx >= g.ax_lo && gx <= g.ax_hi;
         o.x = (ract && act[0]) ? o.x : c.x;
         o.y = (ract && act[1]) ? o.y : c.y;
@@ -291,7 +297,7 @@ struct TkBounds {
   static constexpr int min_blocks = (K <= 5) ? 4 : 3;
 };
 
-template <int K, int ARITH>
+template <int K, int ARITH, bool IMM>
 __global__ void __launch_bounds__(TK_WARPS * 32, TkBounds<K>::min_blocks)
 tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
@@ -339,11 +345,11 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
     const bool extras = comm_edge || a.norm != H2D_NORM_NONE;
     if (extras) {
       // Cold variants: one instantiation handles frozen and active footprints.
-      acc = run_task<K, ARITH, true, true>(&tmap, a, strip, chunk, comm_edge, ring, bars, lane);
+      acc = run_task<K, ARITH, IMM, true, true>(&tmap, a, strip, chunk, comm_edge, ring, bars, lane);
     } else if (frozen) {
-      acc = run_task<K, ARITH, true, false>(&tmap, a, strip, chunk, false, ring, bars, lane);
+      acc = run_task<K, ARITH, IMM, true, false>(&tmap, a, strip, chunk, false, ring, bars, lane);
     } else {
-      acc = run_task<K, ARITH, false, false>(&tmap, a, strip, chunk, false, ring, bars, lane);
+      acc = run_task<K, ARITH, IMM, false, false>(&tmap, a, strip, chunk, false, ring, bars, lane);
     }
 
     if (comm_edge) {
@@ -398,27 +404,32 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
 
 typedef void (*tk_fn_t)(const CUtensorMap, const TkArgs);
 
-template <int ARITH>
+template <int ARITH, bool IMM>
 static tk_fn_t tk_pick_k(int k) {
   switch (k) {
-    case 1: return tk_kernel<1, ARITH>;
-    case 2: return tk_kernel<2, ARITH>;
-    case 3: return tk_kernel<3, ARITH>;
-    case 4: return tk_kernel<4, ARITH>;
-    case 5: return tk_kernel<5, ARITH>;
-    case 6: return tk_kernel<6, ARITH>;
-    case 7: return tk_kernel<7, ARITH>;
-    case 8: return tk_kernel<8, ARITH>;
+    case 1: return tk_kernel<1, ARITH, IMM>;
+    case 2: return tk_kernel<2, ARITH, IMM>;
+    case 3: return tk_kernel<3, ARITH, IMM>;
+    case 4: return tk_kernel<4, ARITH, IMM>;
+    case 5: return tk_kernel<5, ARITH, IMM>;
+    case 6: return tk_kernel<6, ARITH, IMM>;
+    case 7: return tk_kernel<7, ARITH, IMM>;
+    case 8: return tk_kernel<8, ARITH, IMM>;
     default: return nullptr;
   }
 }
-static tk_fn_t tk_pick(int k, int arith) {
+// `imm`: fp32 mode with exactly the reference coefficients -> immediate-operand kernels.
+static tk_fn_t tk_pick(int k, int arith, bool imm) {
   switch (arith) {
-    case H2D_ARITH_FP32: return tk_pick_k<H2D_ARITH_FP32>(k);
-    case H2D_ARITH_STRICT: return tk_pick_k<H2D_ARITH_STRICT>(k);
-    case H2D_ARITH_STRICT_FMA: return tk_pick_k<H2D_ARITH_STRICT_FMA>(k);
+    case H2D_ARITH_FP32: return imm ? tk_pick_k<H2D_ARITH_FP32, true>(k) : tk_pick_k<H2D_ARITH_FP32, false>(k);
+    case H2D_ARITH_STRICT: return tk_pick_k<H2D_ARITH_STRICT, false>(k);
+    case H2D_ARITH_STRICT_FMA: return tk_pick_k<H2D_ARITH_STRICT_FMA, false>(k);
     default: return nullptr;
   }
+}
+
+static bool coef_is_reference(const Geo& g, int arith) {
+  return arith == H2D_ARITH_FP32 && g.cx == kRefCx && g.cy == kRefCy && g.a0 == kRefA0;
 }
 
 }  // namespace h2d
@@ -637,7 +648,7 @@ h2d_plan_t* h2d_plan_create(const h2d_plan_desc_t* d) {
   }
   // Opt in to the dynamic shared memory size once per kernel variant.
   for (int k = 1; k <= d->kmax; ++k) {
-    tk_fn_t fn = tk_pick(k, d->phys.arith);
+    tk_fn_t fn = tk_pick(k, d->phys.arith, coef_is_reference(p->geo, d->phys.arith));
     cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, TK_SMEM_BYTES);
   }
   return p;
@@ -650,7 +661,7 @@ int h2d_plan_launch(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int no
     return h2d_fail(H2D_EINVAL, "h2d_plan_launch: k = %d outside [1, kmax = %d]", k, p->desc.kmax);
   if (norm < H2D_NORM_NONE || norm > H2D_NORM_LINF)
     return h2d_fail(H2D_EINVAL, "h2d_plan_launch: unknown norm %d", norm);
-  tk_fn_t fn = tk_pick(k, p->desc.phys.arith);
+  tk_fn_t fn = tk_pick(k, p->desc.phys.arith, coef_is_reference(p->geo, p->desc.phys.arith));
   if (!fn) return h2d_fail(H2D_EINVAL, "h2d_plan_launch: no kernel for k = %d", k);
   const int H = round_up4(k);
   const TaskList& tl = p->lists[H / 4];

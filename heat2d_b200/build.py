@@ -87,9 +87,16 @@ def build_cpu(force=False, verbose=False) -> Path:
 
 
 def build_cuda(force=False, verbose=False) -> Path:
+    # Experiment hook: H2D_VARIANT=name H2D_NVCC_EXTRA="-DFOO=1" builds
+    # libheat2d_cuda_name.so next to the default library (tools/ only).
+    variant = os.environ.get("H2D_VARIANT", "")
+    extra = os.environ.get("H2D_NVCC_EXTRA", "").split()
+    global OBJ
     LIB.mkdir(parents=True, exist_ok=True)
+    obj_dir = LIB / ("obj_" + variant if variant else "obj")
+    OBJ = obj_dir
     OBJ.mkdir(parents=True, exist_ok=True)
-    out = LIB / "libheat2d_cuda.so"
+    out = LIB / ("libheat2d_cuda_%s.so" % variant if variant else "libheat2d_cuda.so")
     srcs = [CSRC / s for s in CUDA_SOURCES]
     hdrs = _headers()
     if not force and _newer(out, srcs + hdrs):
@@ -100,7 +107,7 @@ def build_cuda(force=False, verbose=False) -> Path:
         obj = OBJ / (src.stem + ".o")
         if not force and _newer(obj, [src] + hdrs):
             return obj
-        cmd = [nvcc, *NVCC_FLAGS, f"-I{INC}", f"-I{CSRC}", "-c", str(src), "-o", str(obj)]
+        cmd = [nvcc, *NVCC_FLAGS, *extra, f"-I{INC}", f"-I{CSRC}", "-c", str(src), "-o", str(obj)]
         _run(cmd, verbose, log_path=OBJ / (src.stem + ".ptxas.log"))
         return obj
 

@@ -229,3 +229,16 @@ def test_plain_kernel_reads_ghosts_of_all_four_neighbours(px, py):
         K.step_plain(f.buf[0], f.buf[1], f.tile, phys)
         got[spec.x0:spec.x0 + spec.rows, spec.y0:spec.y0 + spec.cols] = f.owned(1).cpu().numpy()
     assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("cx,cy", [(0.07, 0.13), (0.2, 0.05)])
+def test_tk_kernel_general_coefficients(cx, cy):
+    # cx = cy = 0.1 takes the immediate-operand kernels; everything else the register form
+    nx, ny = 200, 300
+    u0 = rand_grid(nx, ny, 17)
+    cfg = HeatConfig(nx=nx, ny=ny, steps=24, k=8, cx=cx, cy=cy, chunk_rows=32)
+    s = Heat2DSolver(cfg, DEV).load(u0)
+    s.run()
+    ref = u0.copy()
+    K.cpu_run(ref, 24, N.make_phys(cx, cy, "fixed", "fp32"))
+    assert np.array_equal(s.gather().numpy(), ref)
