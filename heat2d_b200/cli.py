@@ -1,0 +1,226 @@
+"""Command line: the reference's compile-time macros as runtime flags.
+
+    python -m heat2d_b200 --nx 2560 --ny 2048 --steps 1000 -k 8
+    torchrun --nproc-per-node 8 -m heat2d_b200 --nx 32768 --ny 32768 --px 2 --py 4 --steps 1000
+    python -m heat2d_b200 --preset grad1612_mpi --backend cpu --out-dir out
+
+Stdout keeps the reference's lines (problem size, per-rank tile, iteration count,
+``Elapsed time: %e sec``); a JSON record goes to ``<out-dir>/result.json``.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+from .config import BACKENDS, CONV_MODES, HeatConfig, ConfigError
+
+
+def build_parser() -> argparse.ArgumentParser:
+    ap = argparse.ArgumentParser(prog="heat2d_b200", description=__doc__,
+                                 formatter_class=argparse.RawDescriptionHelpFormatter)
+    d = HeatConfig()
+    ap.add_argument("--preset", choices=["mpi_heat2Dn", "grad1612_mpi", "grad1612_hybrid", "grad1612_cuda"],
+                    help="start from one reference program's #define block")
+    ap.add_argument("--nx", type=int, help=f"NXPROB: rows (default {d.nx})")
+    ap.add_argument("--ny", type=int, help=f"NYPROB: columns (default {d.ny})")
+    ap.add_argument("--steps", type=int, help=f"STEPS (default {d.steps})")
+    ap.add_argument("--px", type=int, help="GRIDX: tiles along x (rows)")
+    ap.add_argument("--py", type=int, help="GRIDY: tiles along y (columns)")
+    ap.add_argument("--conv", choices=["on", "off"], help="CONVERGENCE")
+    ap.add_argument("--interval", type=int, help="INTERVAL (default 20)")
+    ap.add_argument("--eps", type=float, help="SENSITIVITY (default 0.1)")
+    ap.add_argument("--norm", choices=["l2sq", "linf"], help="l2sq = reference; linf = max |du|")
+    ap.add_argument("--conv-mode", choices=CONV_MODES)
+    ap.add_argument("--ref-conv-bug", action="store_true",
+                    help="replay the shipped predicate `i %% INTERVAL` (grad1612_mpi_heat.c:263): "
+                         "checks every step iff (nx/px) %% interval == 0, else never")
+    ap.add_argument("--cx", type=float)
+    ap.add_argument("--cy", type=float)
+    ap.add_argument("--cx-float", action="store_true", help="coefficients stored as float (mpi_heat2Dn.c:41-44)")
+    ap.add_argument("--boundary", choices=["fixed", "ghost-ring"])
+    ap.add_argument("--arith", choices=["fp32", "strict", "strict-fma"])
+    ap.add_argument("--init", choices=["ref-int32", "ref-uint32", "exact", "zero"])
+    ap.add_argument("--dump", help="comma list of none|prtdat|rowmajor|binary")
+    ap.add_argument("--out-dir")
+    ap.add_argument("-k", type=int, help="time steps per launch / halo exchange (1..8)")
+    ap.add_argument("--backend", choices=BACKENDS)
+    ap.add_argument("--chunk-rows", type=int)
+    ap.add_argument("--threads", type=int, help="NUMTHREADS (cpu backend)")
+    ap.add_argument("--no-uneven", action="store_true", help="insist on exact divisibility (grad1612_mpi_heat.c:60)")
+    ap.add_argument("--restart", help="raw fp32 nx*ny file (final_binary.dat) to start from")
+    ap.add_argument("--start-step", type=int, help="step index the restart file corresponds to")
+    ap.add_argument("--debug", action="store_true", help="DEBUG: neighbours per rank, device properties")
+    return ap
+
+
+def config_from_args(a) -> HeatConfig:
+    if a.preset:
+        from .models.presets import preset
+        cfg = preset(a.preset)
+    else:
+        cfg = HeatConfig()
+    over = {}
+    for name in ("nx", "ny", "steps", "px", "py", "interval", "eps", "norm", "cx", "cy", "boundary", "arith",
+                 "init", "dump", "out_dir", "k", "backend", "chunk_rows", "threads", "restart", "start_step",
+                 "conv_mode"):
+        v = getattr(a, name, None)
+        if v is not None:
+            over[name] = v
+    if a.conv is not None:
+        over["conv"] = a.conv == "on"
+    if a.cx_float:
+        over["cx_float"] = True
+    if a.no_uneven:
+        over["uneven"] = False
+    if a.debug:
+        over["debug"] = True
+    if a.ref_conv_bug:
+        over["ref_conv_bug"] = True
+    cfg = cfg.replace(**over)
+    if cfg.halo < cfg.k:
+        cfg = cfg.replace(halo=cfg.k)
+    return cfg
+
+
+def _banner(cfg: HeatConfig, world: int, style: str):
+    if style == "mpi_heat2Dn":
+        print(f"Starting mpi_heat2D with {world} worker tasks.")
+        print(f"Grid size: X= {cfg.nx}  Y= {cfg.ny}  Time steps= {cfg.steps}")
+    elif style == "grad1612_cuda":
+        print(f"Problem size: {cfg.nx}x{cfg.ny}\nAmount of iterations: {cfg.steps}")
+    else:
+        print(f"Starting with {world} processes\nProblem size:{cfg.nx}x{cfg.ny}\n"
+              f"Each process will take: {cfg.nx // cfg.px}x{cfg.ny // cfg.py}\nAmount of iterations: {cfg.steps}")
+        if cfg.conv:
+            print(f"Check for convergence every {cfg.interval} iterations")
+
+
+def main(argv=None) -> int:
+    a = build_parser().parse_args(argv)
+    try:
+        cfg = config_from_args(a)
+        dumps = [d for d in cfg.dump.split(",") if d and d != "none"]
+        for dname in dumps:
+            if dname not in ("prtdat", "rowmajor", "binary"):
+                raise ConfigError(f"unknown dump format {dname!r}")
+        cfg = cfg.replace(dump="none")  # dumps are handled here, formats validated above
+        if cfg.ref_conv_bug and cfg.conv:
+            # the stale loop variable equals the tile height after the interior sweep
+            fires = (cfg.nx // cfg.px) % cfg.interval == 0
+            cfg = cfg.replace(interval=1) if fires else cfg.replace(conv=False)
+    except (ConfigError, KeyError, ValueError) as e:
+        print(str(e), file=sys.stderr)
+        print("Quitting...", file=sys.stderr)
+        return 1
+
+    import numpy as np
+    import torch
+    rank, world = 0, 1
+    solver = None
+    if cfg.backend != "cpu":
+        from .parallel.dist import init_distributed
+        rank, world, local, device = init_distributed()
+        if not torch.cuda.is_available() and cfg.backend != "nccl-halo":
+            print("no CUDA device: use --backend cpu (oracle) or --backend nccl-halo under torchrun",
+                  file=sys.stderr)
+            return 1
+    try:
+        if cfg.backend not in ("cpu", "single", "resident", "plain") or world > 1:
+            cfg.validate(world_size=world if world > 1 or cfg.backend == "nccl-halo" else None)
+        from .api import make_solver
+        solver = make_solver(cfg)
+    except (ConfigError, ValueError) as e:
+        if rank == 0:
+            print(str(e), file=sys.stderr)
+            print("Quitting...", file=sys.stderr)
+        return 1
+
+    from .utils import dump as D
+    style = a.preset or "grad1612_mpi"
+    if rank == 0:
+        _banner(cfg, world if world > 1 else cfg.px * cfg.py, style)
+    if cfg.debug:
+        from .parallel.decomp import Decomposition
+        dec = Decomposition(cfg.nx, cfg.ny, cfg.px, cfg.py, cfg.uneven)
+        t = dec.tile(rank if world > 1 else 0)
+        nb = t.neighbours
+        print(f"I am {rank} and my neighbors are North={nb['N']}, South={nb['S']}, East={nb['E']}, "
+              f"West={nb['W']} (Running on {os.uname().nodename})")
+        if rank == 0 and torch.cuda.is_available():
+            from .ops import kernels as K
+            print(K.device_info(torch.cuda.current_device()))
+
+    if cfg.restart:
+        grid = D.read_binary(cfg.restart, cfg.nx, cfg.ny)
+        solver.load(grid)
+    else:
+        solver.initialize()
+
+    def write(stem):
+        if not dumps:
+            return
+        os.makedirs(cfg.out_dir, exist_ok=True)
+        field = solver.gather()
+        if rank != 0:
+            return
+        for dname in dumps:
+            if rank == 0 and stem == "initial" and style != "grad1612_cuda":
+                pass
+            if dname == "binary":
+                D.write_binary(os.path.join(cfg.out_dir, f"{stem}_binary.dat"), field, truncate=False)
+            elif dname == "prtdat":
+                D.write_prtdat(os.path.join(cfg.out_dir, f"{stem}.dat"), field)
+            else:
+                D.write_rowmajor(os.path.join(cfg.out_dir, f"{stem}.dat"), field)
+
+    if rank == 0 and dumps:
+        print("Writing initial.dat ..." if style != "mpi_heat2Dn"
+              else "Initializing grid and writing initial.dat file...")
+    write("initial")
+    res = solver.run()
+    if rank == 0:
+        if style == "mpi_heat2Dn":
+            print(f"Elapsed time: {res.elapsed_s:e} sec")
+            if dumps:
+                print("Writing final.dat file and generating graph...")
+        elif style == "grad1612_cuda":
+            print(f"Elapsed time: {res.elapsed_s:e} sec")
+        else:
+            print(f"Exiting after {res.iterations} iterations\nElapsed time: {res.elapsed_s:e} sec")
+            if dumps:
+                print("Writing final.dat ...")
+    write("final")
+    if rank == 0:
+        rec = {"config": cfg.to_dict(), "world": world, "steps_done": res.steps_done,
+               "iterations": res.iterations, "converged": res.converged, "last_norm": res.last_norm,
+               "seconds_max_over_ranks": res.elapsed_s, "glups": res.glups, "launches": res.launches,
+               "checks": res.checks, "when": time.strftime("%Y-%m-%dT%H:%M:%S")}
+        try:
+            with open(os.path.join(os.path.dirname(os.path.dirname(__file__)), "MEASURED_PEAKS.json")) as f:
+                hbm = json.load(f).get("hbm_gbs")
+            if hbm and cfg.backend not in ("cpu",):
+                rec["pct_of_k1_hbm_roofline"] = 100.0 * res.glups / (hbm / 8.0 * max(world, 1))
+        except Exception:  # noqa: BLE001
+            pass
+        os.makedirs(cfg.out_dir, exist_ok=True)
+        with open(os.path.join(cfg.out_dir, "result.json"), "w") as f:
+            json.dump(rec, f, indent=1)
+        print(f"{res.glups:.3f} GLUP/s")
+    close = getattr(solver, "close", None)
+    if close:
+        close()
+    try:
+        import torch.distributed as dist
+        if dist.is_initialized():
+            dist.barrier()
+            dist.destroy_process_group()
+    except Exception:  # noqa: BLE001
+        pass
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

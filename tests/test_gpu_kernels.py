@@ -242,3 +242,21 @@ def test_tk_kernel_general_coefficients(cx, cy):
     ref = u0.copy()
     K.cpu_run(ref, 24, N.make_phys(cx, cy, "fixed", "fp32"))
     assert np.array_equal(s.gather().numpy(), ref)
+
+
+def test_cli_gpu(tmp_path):
+    import json
+    import subprocess
+    import sys
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "heat2d_b200", "--nx", "640", "--ny", "512", "--steps", "100",
+                        "-k", "8", "--px", "2", "--py", "2", "--dump", "binary", "--debug", "--out-dir", str(tmp_path)],
+                       cwd=root, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert "Problem size:640x512" in r.stdout and "Each process will take: 320x256" in r.stdout
+    assert "Elapsed time:" in r.stdout
+    got = np.fromfile(str(tmp_path / "final_binary.dat"), dtype=np.float32).reshape(640, 512)
+    assert np.array_equal(got, oracle(640, 512, 100))
+    rec = json.loads((tmp_path / "result.json").read_text())
+    assert rec["launches"] > 0 and rec["steps_done"] == 100
