@@ -112,6 +112,79 @@ def run_cuda(exe: Path, gpu: int = 0, timeout: float = 3600.0) -> float:
     return float(m.group(1))
 
 
+SHIM_SRC = HERE / "mpishim"
+SHIM = REF / "shim"
+
+
+def _gcc() -> str:
+    for cand in ("/usr/bin/gcc", os.environ.get("CC"), shutil.which("gcc")):
+        if cand and Path(cand).exists():
+            return cand
+    raise RuntimeError("gcc not found")
+
+
+def build_shim(force: bool = False) -> Path:
+    """Build the single-node MPI shim (baseline/mpishim) into baseline/_ref/shim/."""
+    SHIM.mkdir(parents=True, exist_ok=True)
+    lib, exe = SHIM / "libmpi.a", SHIM / "mpiexec"
+    srcs = [SHIM_SRC / "mpishim.c", SHIM_SRC / "mpiexec.c", SHIM_SRC / "mpi.h"]
+    if not force and lib.exists() and exe.exists() and \
+            min(lib.stat().st_mtime, exe.stat().st_mtime) >= max(f.stat().st_mtime for f in srcs):
+        return SHIM
+    cc = _gcc()
+    obj = SHIM / "mpishim.o"
+    for cmd in ([cc, "-O2", "-Wall", f"-I{SHIM_SRC}", "-c", str(SHIM_SRC / "mpishim.c"), "-o", str(obj)],
+                ["ar", "rcs", str(lib), str(obj)],
+                [cc, "-O2", "-Wall", str(SHIM_SRC / "mpiexec.c"), "-o", str(exe)]):
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("shim build failed:\n" + r.stdout + r.stderr)
+    return SHIM
+
+
+MPI_PROGRAMS = {"mpi_heat2Dn": "mpi_heat2Dn.c", "grad1612_mpi": "grad1612_mpi_heat.c",
+                "grad1612_hybrid": "grad1612_hybrid_heat.c"}
+
+
+def build_mpi(program: str, defines: dict, opt: str = "-O3") -> Path:
+    """One of the three MPI reference programs on the shim.  `opt` replaces the
+    README's ``-g`` (readme.md:10,14); the mpiP build of the report used -O3."""
+    if not staged():
+        stage()
+    build_shim()
+    fname = MPI_PROGRAMS[program]
+    tag = program + "_" + "_".join(f"{k}{v}" for k, v in sorted(defines.items())) + "_" + opt.strip("-")
+    BIN.mkdir(parents=True, exist_ok=True)
+    exe = BIN / tag
+    if exe.exists():
+        return exe
+    src = configure(fname, defines, tag)
+    cmd = [_gcc(), opt, "-Wall", "-Wno-unused-result", "-Wno-unused-variable", "-Wno-implicit-int",
+           "-Wno-unused-but-set-variable", "-Wno-maybe-uninitialized", "-Wno-deprecated-non-prototype",
+           f"-I{SHIM_SRC}", str(src), str(SHIM / "libmpi.a"), "-o", str(exe)]
+    if program == "grad1612_hybrid":
+        cmd.insert(2, "-fopenmp")
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("reference MPI build failed:\n" + r.stdout + r.stderr)
+    return exe
+
+
+def run_mpi(exe: Path, nproc: int, cwd, timeout: float = 3600.0, env_extra=None):
+    """mpiexec -n nproc exe, in `cwd` (the programs write initial.dat / final.dat there).
+    Returns (stdout, elapsed seconds printed by the program or None)."""
+    build_shim()
+    env = dict(os.environ)
+    if env_extra:
+        env.update(env_extra)
+    r = subprocess.run([str(SHIM / "mpiexec"), "-n", str(nproc), str(exe)], capture_output=True, text=True,
+                       timeout=timeout, cwd=str(cwd), env=env)
+    if r.returncode != 0:
+        raise RuntimeError(f"{exe.name} on {nproc} ranks exited {r.returncode}:\n{r.stdout[-2000:]}{r.stderr[-2000:]}")
+    m = re.search(r"Elapsed time:\s*([0-9.eE+-]+)\s*sec", r.stdout)
+    return r.stdout, (float(m.group(1)) if m else None)
+
+
 def main(argv=None):
     import argparse
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)

@@ -79,8 +79,9 @@ class HeatConfig:
                 raise ConfigError(f"{name} must be one of {sorted(table)}")
         if self.backend not in BACKENDS:
             raise ConfigError(f"backend must be one of {BACKENDS}")
-        if self.dump not in DUMPS:
-            raise ConfigError(f"dump must be one of {DUMPS}")
+        for dname in self.dump.split(","):
+            if dname not in DUMPS:
+                raise ConfigError(f"dump must be a comma list of {DUMPS}")
         if self.conv_mode not in CONV_MODES:
             raise ConfigError(f"conv_mode must be one of {CONV_MODES}")
         if not 1 <= self.k <= KMAX:
