@@ -705,6 +705,18 @@ int h2d_plan_launch(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int no
   return H2D_OK;
 }
 
+int h2d_plan_run_many(h2d_plan_t* const* plans, int n_plans, int src_parity, int k, int n_launches,
+                      uint32_t epoch0, void* stream) {
+  if (!plans || n_plans < 1 || n_launches < 0) return h2d_fail(H2D_EINVAL, "h2d_plan_run_many: bad argument");
+  int par = src_parity;
+  for (int l = 0; l < n_launches; ++l) {
+    for (int i = 0; i < n_plans; ++i)
+      if (int rc = h2d_plan_launch(plans[i], par, k, epoch0 + (uint32_t)l, H2D_NORM_NONE, stream)) return rc;
+    par ^= 1;
+  }
+  return H2D_OK;
+}
+
 int64_t h2d_plan_launch_count(const h2d_plan_t* p) { return p ? p->launches : 0; }
 float* h2d_plan_norm_ptr(h2d_plan_t* p) { return p ? (float*)((unsigned*)p->scratch + 2) : nullptr; }
 uint32_t* h2d_plan_fault_ptr(h2d_plan_t* p) { return p ? (uint32_t*)p->scratch + 3 : nullptr; }

@@ -127,6 +127,7 @@ def cuda():
             lib.h2d_plan_destroy.argtypes = [vp]
             lib.h2d_plan_destroy.restype = None
             lib.h2d_plan_launch.argtypes = [vp, C.c_int, C.c_int, C.c_uint32, C.c_int, vp]
+            lib.h2d_plan_run_many.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32, vp]
             lib.h2d_plan_launch_count.argtypes = [vp]
             lib.h2d_plan_launch_count.restype = C.c_int64
             lib.h2d_plan_norm_ptr.argtypes = [vp]

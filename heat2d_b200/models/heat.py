@@ -295,8 +295,23 @@ class Heat2DSolver:
         iterations = None
         with torch.cuda.device(self.device):
             ev0.record()
-            for L in sched:
+            i = 0
+            while i < len(sched):
+                L = sched[i]
                 check = L.check and cfg.conv
+                if not check and cfg.backend != "plain":
+                    # a stretch of identical launches goes to the device in one native call
+                    j = i
+                    while j < len(sched) and sched[j].k == L.k and not (sched[j].check and cfg.conv):
+                        j += 1
+                    n = j - i
+                    K.Plan.run_many([e.plan for e in self.engines], self.parity, L.k, n, self.epoch + 1)
+                    self.epoch += n
+                    launches += n * len(self.engines)
+                    self.parity ^= n & 1
+                    self.steps_done += n * L.k
+                    i = j
+                    continue
                 self._launch_all(L, norm if check else "none")
                 launches += 1 if cfg.backend == "plain" else len(self.engines)
                 if check:
@@ -314,6 +329,7 @@ class Heat2DSolver:
                         break
                 self.parity ^= 1
                 self.steps_done += L.k
+                i += 1
             ev1.record()
             ev1.synchronize()
         self._check_faults()

@@ -201,6 +201,16 @@ class Plan:
             N.check(self._lib, self._lib.h2d_plan_launch(self._h, src_parity, k, epoch & 0xFFFFFFFF,
                                                          N.NORM[norm], _stream_ptr(self.device)))
 
+    @staticmethod
+    def run_many(plans, src_parity: int, k: int, n_launches: int, epoch0: int):
+        """`n_launches` back-to-back k-step launches of every plan in `plans` (one
+        native call: the per-launch cost is the bare cudaLaunchKernel)."""
+        lib = plans[0]._lib
+        arr = (C.c_void_p * len(plans))(*[p._h for p in plans])
+        with torch.cuda.device(plans[0].device):
+            N.check(lib, lib.h2d_plan_run_many(arr, len(plans), src_parity, k, n_launches,
+                                               epoch0 & 0xFFFFFFFF, _stream_ptr(plans[0].device)))
+
     @property
     def launch_count(self) -> int:
         return int(self._lib.h2d_plan_launch_count(self._h))

@@ -197,6 +197,16 @@ void h2d_plan_destroy(h2d_plan_t* plan);
 int h2d_plan_launch(h2d_plan_t* plan, int src_parity, int k, uint32_t epoch, int norm,
                     void* stream);
 
+/* `n_launches` consecutive k-step launches without going back to the caller:
+ * launch l uses epoch0 + l and alternates the source parity starting from
+ * `src_parity`; with several plans (tiles emulated in one process) each launch
+ * index is issued for every plan before the next one starts.  Small grids are
+ * bound by the per-launch host cost, which this keeps at the bare
+ * cudaLaunchKernel (the reference pays one host launch per time step,
+ * grad1612_cuda_heat.cu:82-85).                                               */
+int h2d_plan_run_many(h2d_plan_t* const* plans, int n_plans, int src_parity, int k, int n_launches,
+                      uint32_t epoch0, void* stream);
+
 /* Number of kernels launched by this plan since creation (bench bookkeeping). */
 int64_t h2d_plan_launch_count(const h2d_plan_t* plan);
 /* Device address of this rank's partial norm (1 float, valid after a launch
