@@ -119,6 +119,8 @@ def main():
     from heat2d_b200.utils.clocks import ClockSampler
 
     rank, world, local, device = init_distributed()
+    from heat2d_b200.utils.numa import bind_to_gpu_numa
+    numa = bind_to_gpu_numa(local)      # pinned host buffers next to the GPU
     if world != a.gpus and world > 1:
         raise SystemExit(f"--gpus {a.gpus} but WORLD_SIZE={world}")
     n = a.grid
@@ -204,7 +206,7 @@ def main():
                        "parallelism": f"{px}x{py} tiles (rows x cols), one per GPU",
                        "k": k, "backend": a.impl, "conv": bool(a.conv),
                        "l2": f"inputs larger than L2 ({n * n * 4 / world / 2**20:.0f} MiB per GPU per buffer vs 126 MiB)"},
-            "clocks": cs.summary(), "gpu_launches": launches, "impl": a.impl,
+            "clocks": cs.summary(), "gpu_launches": launches, "impl": a.impl, "numa": numa,
             "baseline_ref": "10.1 GLUP/s = best published reference number (grad1612 MPI, 2560x2048, 160 ranks, "
                             "Report.pdf p21); published CUDA number is 0.669 GLUP/s",
             "roofline": {"hbm_gbs_measured": _peaks().get("hbm_gbs"),

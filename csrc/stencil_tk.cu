@@ -24,6 +24,7 @@
 // (up, centre) in registers, so the state is 2*4*K floats per lane.
 #include <cuda.h>
 #include <cstdio>
+#include <cmath>
 #include <cstring>
 #include <type_traits>
 #include <vector>
@@ -461,16 +462,41 @@ struct h2d_plan {
 
 static inline int round_up4(int k) { return (k + 3) & ~3; }
 
+static int g_sm_count = 0;
+static int sm_count() {
+  if (g_sm_count <= 0) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
+      g_sm_count = n;
+    else
+      g_sm_count = 148;
+  }
+  return g_sm_count;
+}
+
 static int choose_chunk_rows(int rows, int cols, int kmax) {
-  // Long chunks keep the 2K-row pipeline fill at a few per cent (R = 512, K = 8:
-  // 3 %), but there must be enough tasks for a couple of waves of
-  // 148 SMs x 12..16 resident warps.
+  // Tasks cost about the same and the block scheduler hands them out in order,
+  // so a launch takes about ceil(tasks / slots) "waves" of one task time, and a
+  // task time is proportional to the rows it streams, R + 2K (K rows of pipeline
+  // fill at both ends).  Half a wave is added for the slower edge / boundary
+  // tasks.  Minimise  (ceil(waves) + 0.5) * (R + 2K)  over the chunk count.
+  // slots = SMs x resident warps (16 up to K = 5, 12 beyond: register-limited).
+  // Small grids land in the latency regime (one wave): short chunks win there.
   const int wv = TK_W - 2 * round_up4(kmax);
   const int n_strips = (cols + wv - 1) / wv;
-  int R = 512;
-  while (R > 32 && (int64_t)(rows / R) * n_strips < 3 * 148 * 16) R >>= 1;
-  if (R < kmax) R = kmax;
-  return R;
+  const double slots = (double)sm_count() * (kmax <= 5 ? 16 : 12);
+  const int r_min = kmax > 8 ? kmax : 8;
+  int best_R = rows;
+  double best = 1e300;
+  for (int c = 1; c <= rows; ++c) {
+    const int R = rows / c;
+    if (R < r_min && c > 1) break;
+    const double waves = ceil((double)(rows / R) * n_strips / slots);
+    const double t = (waves + 0.5) * (double)(R + 2 * kmax);
+    if (t < best * (1.0 - 1e-9)) { best = t; best_R = R; }
+  }
+  return best_R;
 }
 
 static void plan_counts(const h2d_tile_t* t, int kmax, int chunk_rows, int* n_chunks,
