@@ -23,7 +23,14 @@ namespace h2d {
 __global__ void norm_finish_kernel(const float* local_val, float* const* vals,
                                    uint32_t* const* flags, int rank, int world, uint32_t seq,
                                    int norm, float eps, float* out, uint32_t* stop, int phase,
-                                   int64_t timeout_ns, uint32_t* fault) {
+                                   int64_t timeout_ns, uint32_t* fault, uint32_t* ctl) {
+  // An earlier check already stopped the run: every rank sees the same word.
+  // (In the split-phase emulation the publish phase of check `seq` runs before any
+  // combine phase of the same check, so ctl == seq can only be seen by a combine.)
+  if (ctl != nullptr) {
+    const uint32_t c = *reinterpret_cast<volatile uint32_t*>(ctl);
+    if (c != 0u && c != seq) return;
+  }
   const int par = (int)(seq & 1u);
   if (phase & 1) {
     const float v = *local_val;
@@ -52,7 +59,10 @@ __global__ void norm_finish_kernel(const float* local_val, float* const* vals,
       t = (norm == H2D_NORM_L2SQ) ? t + x : fmaxf(t, x);
     }
     *out = t;
-    if (!failed && t < eps) *stop = 1u;
+    if (!failed && t < eps) {
+      if (stop != nullptr) *stop = 1u;
+      if (ctl != nullptr) *ctl = seq;
+    }
   }
 }
 
@@ -126,11 +136,35 @@ void h2d_arena_destroy(h2d_arena_t* a) {
   delete a;
 }
 
+static int norm_finish_impl(const float* local_val, float* const* vals, uint32_t* const* flags,
+                            int rank, int world, uint32_t seq, int norm, float eps, float* out_dev,
+                            uint32_t* stop_dev, uint32_t* ctl, int phase, int64_t spin_timeout_ns,
+                            uint32_t* fault_dev, void* stream);
+
 int h2d_cuda_norm_finish(const float* local_val, float* const* vals, uint32_t* const* flags,
                          int rank, int world, uint32_t seq, int norm, float eps, float* out_dev,
                          uint32_t* stop_dev, int phase, int64_t spin_timeout_ns,
                          uint32_t* fault_dev, void* stream) {
-  if (!local_val || !vals || !flags || !out_dev || !stop_dev)
+  if (!stop_dev) return h2d_fail(H2D_EINVAL, "h2d_cuda_norm_finish: null argument");
+  return norm_finish_impl(local_val, vals, flags, rank, world, seq, norm, eps, out_dev, stop_dev, nullptr,
+                          phase, spin_timeout_ns, fault_dev, stream);
+}
+
+int h2d_cuda_norm_finish_ctl(const float* local_val, float* const* vals, uint32_t* const* flags,
+                             int rank, int world, uint32_t seq, int norm, float eps, float* out_dev,
+                             uint32_t* ctl, int phase, int64_t spin_timeout_ns, uint32_t* fault_dev,
+                             void* stream) {
+  if (!ctl) return h2d_fail(H2D_EINVAL, "h2d_cuda_norm_finish_ctl: null ctl");
+  if (seq == 0) return h2d_fail(H2D_EINVAL, "h2d_cuda_norm_finish_ctl: seq must be >= 1");
+  return norm_finish_impl(local_val, vals, flags, rank, world, seq, norm, eps, out_dev, nullptr, ctl, phase,
+                          spin_timeout_ns, fault_dev, stream);
+}
+
+static int norm_finish_impl(const float* local_val, float* const* vals, uint32_t* const* flags,
+                            int rank, int world, uint32_t seq, int norm, float eps, float* out_dev,
+                            uint32_t* stop_dev, uint32_t* ctl, int phase, int64_t spin_timeout_ns,
+                            uint32_t* fault_dev, void* stream) {
+  if (!local_val || !vals || !flags || !out_dev)
     return h2d_fail(H2D_EINVAL, "h2d_cuda_norm_finish: null argument");
   if (world < 1 || rank < 0 || rank >= world)
     return h2d_fail(H2D_EINVAL, "h2d_cuda_norm_finish: rank %d / world %d", rank, world);
@@ -139,7 +173,7 @@ int h2d_cuda_norm_finish(const float* local_val, float* const* vals, uint32_t* c
   const int ph = phase == 0 ? 1 : phase == 1 ? 2 : 3;
   const int64_t to = spin_timeout_ns > 0 ? spin_timeout_ns : 10000000000LL;
   h2d::norm_finish_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(
-      local_val, vals, flags, rank, world, seq, norm, eps, out_dev, stop_dev, ph, to, fault_dev);
+      local_val, vals, flags, rank, world, seq, norm, eps, out_dev, stop_dev, ph, to, fault_dev, ctl);
   H2D_CHECK_LAUNCH("norm_finish_kernel");
   return H2D_OK;
 }

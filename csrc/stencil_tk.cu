@@ -64,6 +64,11 @@ struct TkArgs {
   float* norm_out;
   int64_t timeout_ns;
   uint32_t* fault;
+  // Device-side run control: the launch does nothing unless *ctl == run_if
+  // (ctl == nullptr: always run).  0 = still iterating; q > 0 = the q-th
+  // convergence check stopped the run (set by norm_finish_kernel).
+  const uint32_t* ctl;
+  uint32_t run_if;
 };
 
 // ------------------------------------------------------------ PTX wrappers
@@ -307,6 +312,10 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ float cta_red[TK_WARPS];
   __shared__ bool cta_last;
+  // Converged earlier (or a conditional launch whose condition did not occur):
+  // every CTA of every rank reads the same word and leaves; no flag is
+  // published and none is awaited, so the ranks stay consistent.
+  if (a.ctl != nullptr && *reinterpret_cast<const volatile uint32_t*>(a.ctl) != a.run_if) return;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int task = (int)blockIdx.x * TK_WARPS + warp;
   const uint32_t ring = smem_u32(smem) + warp * (TK_STAGES * TK_STAGE_BYTES);
@@ -490,9 +499,9 @@ static int choose_chunk_rows(int rows, int cols, int kmax) {
   int best_R = rows;
   double best = 1e300;
   for (int c = 1; c <= rows; ++c) {
-    const int R = rows / c;
+    const int R = (rows + c - 1) / c;   // equal chunks; the last one may be shorter
     if (R < r_min && c > 1) break;
-    const double waves = ceil((double)(rows / R) * n_strips / slots);
+    const double waves = ceil((double)((rows + R - 1) / R) * n_strips / slots);
     const double t = (waves + 0.5) * (double)(R + 2 * kmax);
     if (t < best * (1.0 - 1e-9)) { best = t; best_R = R; }
   }
@@ -502,7 +511,7 @@ static int choose_chunk_rows(int rows, int cols, int kmax) {
 static void plan_counts(const h2d_tile_t* t, int kmax, int chunk_rows, int* n_chunks,
                         int* max_tasks) {
   int R = chunk_rows > 0 ? chunk_rows : choose_chunk_rows(t->rows, t->cols, kmax);
-  int nc = t->rows / R;
+  int nc = (t->rows + R - 1) / R;
   if (nc < 1) nc = 1;
   *n_chunks = nc;
   int mt = 0;
@@ -684,6 +693,11 @@ h2d_plan_t* h2d_plan_create(const h2d_plan_desc_t* d) {
 }
 
 int h2d_plan_launch(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int norm, void* stream) {
+  return h2d_plan_launch_ex(p, src_parity, k, epoch, norm, nullptr, 0u, stream);
+}
+
+int h2d_plan_launch_ex(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int norm,
+                       const uint32_t* ctl, uint32_t run_if, void* stream) {
   if (!p) return h2d_fail(H2D_EINVAL, "h2d_plan_launch: null plan");
   if (src_parity != 0 && src_parity != 1) return h2d_fail(H2D_EINVAL, "h2d_plan_launch: bad parity");
   if (k < 1 || k > p->desc.kmax)
@@ -726,6 +740,8 @@ int h2d_plan_launch(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int no
   a.cta_partials = (float*)((char*)p->scratch + 256);
   a.norm = norm;
   a.timeout_ns = p->desc.spin_timeout_ns > 0 ? p->desc.spin_timeout_ns : 10000000000LL;
+  a.ctl = ctl;
+  a.run_if = run_if;
 
   const int grid = (tl.n_tasks + TK_WARPS - 1) / TK_WARPS;
   fn<<<grid, TK_WARPS * 32, TK_SMEM_BYTES, (cudaStream_t)stream>>>(p->tmap[src_parity], a);
@@ -735,12 +751,14 @@ int h2d_plan_launch(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int no
 }
 
 int h2d_plan_run_many(h2d_plan_t* const* plans, int n_plans, int src_parity, int k, int n_launches,
-                      uint32_t epoch0, void* stream) {
+                      uint32_t epoch0, const uint32_t* const* ctls, void* stream) {
   if (!plans || n_plans < 1 || n_launches < 0) return h2d_fail(H2D_EINVAL, "h2d_plan_run_many: bad argument");
   int par = src_parity;
   for (int l = 0; l < n_launches; ++l) {
     for (int i = 0; i < n_plans; ++i)
-      if (int rc = h2d_plan_launch(plans[i], par, k, epoch0 + (uint32_t)l, H2D_NORM_NONE, stream)) return rc;
+      if (int rc = h2d_plan_launch_ex(plans[i], par, k, epoch0 + (uint32_t)l, H2D_NORM_NONE,
+                                      ctls ? ctls[i] : nullptr, 0u, stream))
+        return rc;
     par ^= 1;
   }
   return H2D_OK;

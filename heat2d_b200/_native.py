@@ -127,7 +127,9 @@ def cuda():
             lib.h2d_plan_destroy.argtypes = [vp]
             lib.h2d_plan_destroy.restype = None
             lib.h2d_plan_launch.argtypes = [vp, C.c_int, C.c_int, C.c_uint32, C.c_int, vp]
-            lib.h2d_plan_run_many.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32, vp]
+            lib.h2d_plan_launch_ex.argtypes = [vp, C.c_int, C.c_int, C.c_uint32, C.c_int, vp, C.c_uint32, vp]
+            lib.h2d_plan_run_many.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32,
+                                              C.POINTER(vp), vp]
             lib.h2d_plan_launch_count.argtypes = [vp]
             lib.h2d_plan_launch_count.restype = C.c_int64
             lib.h2d_plan_norm_ptr.argtypes = [vp]
@@ -142,6 +144,8 @@ def cuda():
             lib.h2d_cuda_norm_diff_static.argtypes = [vp, vp, P(Tile), C.c_int, vp, vp]
             lib.h2d_cuda_norm_finish.argtypes = [vp, vp, vp, C.c_int, C.c_int, C.c_uint32, C.c_int,
                                                  C.c_float, vp, vp, C.c_int, C.c_int64, vp, vp]
+            lib.h2d_cuda_norm_finish_ctl.argtypes = [vp, vp, vp, C.c_int, C.c_int, C.c_uint32, C.c_int,
+                                                     C.c_float, vp, vp, C.c_int, C.c_int64, vp, vp]
             lib.h2d_cuda_pack_edge.argtypes = [vp, P(Tile), C.c_int, C.c_int, vp, vp]
             lib.h2d_cuda_unpack_ghost.argtypes = [vp, P(Tile), C.c_int, C.c_int, vp, vp]
             lib.h2d_arena_create.argtypes = [C.c_size_t]

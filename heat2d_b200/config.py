@@ -126,42 +126,32 @@ def make_schedule(steps: int, k: int, conv: bool = False, interval: int = 20,
     """Split `steps` time steps into launches of at most `k` steps.
 
     Convergence is evaluated on 0-based step indices that are multiples of
-    `interval` (the intent of ``grad1612_mpi_heat.c:263``).  In ``exact`` mode the
-    checked step is always its own k=1 launch, so that on convergence the
-    pre-step field is still intact in the source buffer (the reference breaks
-    out of the loop before flipping buffers, ``:269-273``).  In ``fused-k`` mode
-    the check rides on the last sub-step of a k-step launch.
+    `interval` (the intent of ``grad1612_mpi_heat.c:263``): a launch always ENDS on
+    a checked step, whose (new - old) norm is reduced inside that launch.
+    `conv_mode` does not change the schedule; it decides what the solver returns
+    on convergence (``exact``: the pre-step field, as the reference;
+    ``fused-k``: the post-step field).
     """
     out = []
     s = start_step
     end = start_step + steps
     while s < end:
-        if conv:
-            nxt = ((s + interval - 1) // interval) * interval  # next checked index >= s
-            if conv_mode == "exact":
-                if nxt == s:
-                    out.append(Launch(1, True, s))
-                    s += 1
-                    continue
-                kk = min(k, nxt - s, end - s)
-                out.append(Launch(kk, False, s))
-                s += kk
-            else:
-                # a launch must END with the checked step (index nxt)
-                if nxt >= end:
-                    kk = min(k, end - s)
-                    out.append(Launch(kk, False, s))
-                    s += kk
-                    continue
-                n = nxt - s + 1
-                while n > k:
-                    out.append(Launch(k, False, s))
-                    s += k
-                    n -= k
-                out.append(Launch(n, True, s))
-                s += n
-        else:
+        if not conv:
             kk = min(k, end - s)
             out.append(Launch(kk, False, s))
             s += kk
+            continue
+        nxt = ((s + interval - 1) // interval) * interval  # next checked index >= s
+        if nxt >= end:
+            kk = min(k, end - s)
+            out.append(Launch(kk, False, s))
+            s += kk
+            continue
+        n = nxt - s + 1  # steps up to and including the checked one: the last launch ends on it
+        while n > k:
+            out.append(Launch(k, False, s))
+            s += k
+            n -= k
+        out.append(Launch(n, True, s))
+        s += n
     return out

@@ -134,6 +134,8 @@ class TileEngine:
         dev = field.device
         self.norm_total = torch.zeros(1, dtype=torch.float32, device=dev)
         self.stop = torch.zeros(1, dtype=torch.int32, device=dev)
+        # run-control word: 0 = iterating, q = check number q stopped the run
+        self.ctl = torch.zeros(1, dtype=torch.int32, device=dev)
         self.plan: Optional[K.Plan] = None
         self.vals_ptrs = None
         self.flags_ptrs = None
@@ -148,18 +150,19 @@ class TileEngine:
         self.flags_ptrs = torch.tensor(all_nflags_ptrs, dtype=torch.int64, device=f.device)
         self._fault = tensor_from_ptr(self.plan.fault_ptr, (1,), torch.int32, f.device)
 
-    def launch(self, parity: int, k: int, epoch: int, norm: str):
-        self.plan.launch(parity, k, epoch, norm)
+    def launch(self, parity: int, k: int, epoch: int, norm: str, run_if: int = 0):
+        self.plan.launch(parity, k, epoch, norm, self.ctl.data_ptr(), run_if)
 
     def finish(self, seq: int, norm: str, eps: float, phase: int):
-        """phase 0 = publish, 1 = combine, 2 = publish + wait + combine."""
+        """phase 0 = publish, 1 = combine, 2 = publish + wait + combine.  On
+        convergence the kernel stores `seq` into the run-control word."""
         lib = N.cuda()
         dev = self.field.device
         with torch.cuda.device(dev):
-            N.check(lib, lib.h2d_cuda_norm_finish(
+            N.check(lib, lib.h2d_cuda_norm_finish_ctl(
                 self.plan.norm_ptr, self.vals_ptrs.data_ptr(), self.flags_ptrs.data_ptr(), self.rank,
                 self.world, seq & 0xFFFFFFFF, N.NORM[norm], float(eps), self.norm_total.data_ptr(),
-                self.stop.data_ptr(), phase, int(self.spin_timeout_s * 1e9), self.plan.fault_ptr,
+                self.ctl.data_ptr(), phase, int(self.spin_timeout_s * 1e9), self.plan.fault_ptr,
                 int(torch.cuda.current_stream(dev).cuda_stream)))
 
     def fault(self) -> int:
@@ -255,88 +258,142 @@ class Heat2DSolver:
         k = 1 if cfg.backend == "plain" else cfg.k
         return make_schedule(steps, k, cfg.conv, cfg.interval, cfg.conv_mode, self.steps_done)
 
-    def _launch_all(self, L: Launch, norm: str):
+    def _finish_all(self, seq: int, norm: str):
+        """Cross-tile finish of check number `seq` (no host synchronisation)."""
         cfg = self.cfg
-        if cfg.backend == "plain":
-            f = self.fields[0]
-            K.step_plain(f.buf[self.parity], f.buf[1 - self.parity], f.tile, self.phys)
-            return
-        self.epoch += 1
-        for e in self.engines:
-            e.launch(self.parity, L.k, self.epoch, norm)
-
-    def _norm_value(self, norm: str) -> float:
-        """Finish the cross-tile reduction and read the decision back (one sync)."""
-        cfg = self.cfg
-        if cfg.backend == "plain":
-            f = self.fields[0]
-            v = K.norm_diff(f.buf[1 - self.parity], f.buf[self.parity], f.tile, norm)
-            return float(v.item())
-        self.norm_seq += 1
-        if self.world == 1:
-            self.engines[0].finish(self.norm_seq, norm, cfg.eps, 2)
-        else:
+        if len(self.engines) == 1:
+            self.engines[0].finish(seq, norm, cfg.eps, 2)
+        else:  # ranks emulated as consecutive launches: publish all, then combine all
             for e in self.engines:
-                e.finish(self.norm_seq, norm, cfg.eps, 0)
+                e.finish(seq, norm, cfg.eps, 0)
             for e in self.engines:
-                e.finish(self.norm_seq, norm, cfg.eps, 1)
-        return float(self.engines[0].norm_total.item())
+                e.finish(seq, norm, cfg.eps, 1)
 
     def run(self, steps: Optional[int] = None) -> RunResult:
         cfg = self.cfg
         steps = cfg.steps if steps is None else steps
         if cfg.backend == "resident":
             return self._run_resident(steps)
+        if cfg.backend == "plain":
+            return self._run_plain(steps)
+        return self._run_fused(steps)
+
+    def _run_fused(self, steps: int) -> RunResult:
+        """Queue the whole run without ever synchronising with the device.
+
+        Convergence is decided on the device: the finish kernel of check q writes q
+        into every rank's run-control word, after which every queued launch is a
+        no-op.  ``conv_mode='exact'`` additionally queues, after each k-step check
+        launch, a (k-1)-step launch from the same source that runs only if that
+        check converged: it regenerates the pre-step field the reference returns
+        (it breaks out of the loop before flipping buffers,
+        ``grad1612_mpi_heat.c:269-273``).  Both share one epoch number: at most one
+        of "conditional launch" and "next ordinary launch" ever executes.
+        """
+        cfg = self.cfg
         sched = self.schedule(steps)
         norm = cfg.norm if cfg.conv else "none"
         ev0 = torch.cuda.Event(enable_timing=True)
         ev1 = torch.cuda.Event(enable_timing=True)
-        converged, last_norm, checks, launches = False, float("nan"), 0, 0
-        iterations = None
+        plans = [e.plan for e in self.engines]
+        ctls = [e.ctl.data_ptr() for e in self.engines]
+        records = {}   # seq -> (parity before, k, first_step, epoch of the check launch, launches so far)
+        launches = 0
+        parity, epoch, done = self.parity, self.epoch, self.steps_done
         with torch.cuda.device(self.device):
+            if cfg.conv:
+                for e in self.engines:
+                    e.ctl.zero_()
             ev0.record()
             i = 0
             while i < len(sched):
                 L = sched[i]
-                check = L.check and cfg.conv
-                if not check and cfg.backend != "plain":
-                    # a stretch of identical launches goes to the device in one native call
+                if not (L.check and cfg.conv):
                     j = i
                     while j < len(sched) and sched[j].k == L.k and not (sched[j].check and cfg.conv):
                         j += 1
                     n = j - i
-                    K.Plan.run_many([e.plan for e in self.engines], self.parity, L.k, n, self.epoch + 1)
-                    self.epoch += n
-                    launches += n * len(self.engines)
-                    self.parity ^= n & 1
-                    self.steps_done += n * L.k
+                    K.Plan.run_many(plans, parity, L.k, n, epoch + 1, ctls if cfg.conv else None)
+                    epoch += n
+                    launches += n * len(plans)
+                    parity ^= n & 1
+                    done += n * L.k
                     i = j
                     continue
-                self._launch_all(L, norm if check else "none")
-                launches += 1 if cfg.backend == "plain" else len(self.engines)
-                if check:
-                    last_norm = self._norm_value(norm)
-                    checks += 1
-                    if last_norm < cfg.eps:
-                        converged = True
-                        if cfg.conv_mode == "exact":
-                            # break before the flip: the pre-step field is the result
-                            iterations = L.first_step
-                        else:
-                            self.parity ^= 1
-                            self.steps_done += L.k
-                            iterations = self.steps_done
-                        break
-                self.parity ^= 1
-                self.steps_done += L.k
+                epoch += 1
+                self.norm_seq += 1
+                seq = self.norm_seq
+                for e in self.engines:
+                    e.launch(parity, L.k, epoch, norm, 0)
+                launches += len(plans)
+                self._finish_all(seq, norm)
+                records[seq] = (parity, L.k, L.first_step, epoch, launches)
+                if cfg.conv_mode == "exact" and L.k > 1:
+                    for e in self.engines:
+                        e.launch(parity, L.k - 1, epoch + 1, "none", seq)
+                parity ^= 1
+                done += L.k
                 i += 1
             ev1.record()
             ev1.synchronize()
+        elapsed = ev0.elapsed_time(ev1) / 1e3
+        converged, last_norm, checks, iterations = False, float("nan"), len(records), None
+        if cfg.conv and records:
+            q = int(self.engines[0].ctl.item())
+            last_norm = float(self.engines[0].norm_total.item())
+            if q != 0:
+                converged = True
+                p0, k, first, ep, nl = records[q]
+                checks = sum(1 for s in records if s <= q)
+                launches = nl
+                if cfg.conv_mode == "exact":
+                    # field after `first + k - 1` updates; the reference reports that index
+                    done = first + k - 1
+                    parity = p0 if k == 1 else 1 - p0
+                    epoch = ep if k == 1 else ep + 1
+                    launches += 0 if k == 1 else len(plans)
+                    iterations = done
+                else:
+                    done = first + k
+                    parity = 1 - p0
+                    epoch = ep
+                    iterations = done
+        self.parity, self.epoch, self.steps_done = parity, epoch, done
         self._check_faults()
         if iterations is None:
             iterations = self.steps_done
-        return RunResult(self.steps_done, iterations, converged, last_norm,
-                         ev0.elapsed_time(ev1) / 1e3, launches, checks, cfg.nx, cfg.ny)
+        return RunResult(self.steps_done, iterations, converged, last_norm, elapsed, launches, checks,
+                         cfg.nx, cfg.ny)
+
+    def _run_plain(self, steps: int) -> RunResult:
+        """Plain one-step kernel + standalone norm kernel, host-side decision (the
+        structure of the reference loop; baseline for the fused path)."""
+        cfg = self.cfg
+        f = self.fields[0]
+        ev0 = torch.cuda.Event(enable_timing=True)
+        ev1 = torch.cuda.Event(enable_timing=True)
+        converged, last_norm, checks, launches, iterations = False, float("nan"), 0, 0, None
+        with torch.cuda.device(self.device):
+            ev0.record()
+            for s in range(self.steps_done, self.steps_done + steps):
+                K.step_plain(f.buf[self.parity], f.buf[1 - self.parity], f.tile, self.phys)
+                launches += 1
+                if cfg.conv and s % cfg.interval == 0:
+                    v = K.norm_diff(f.buf[1 - self.parity], f.buf[self.parity], f.tile, cfg.norm)
+                    last_norm = float(v.item())
+                    launches += 1
+                    checks += 1
+                    if last_norm < cfg.eps:
+                        converged, iterations = True, s
+                        break
+                self.parity ^= 1
+                self.steps_done += 1
+            ev1.record()
+            ev1.synchronize()
+        if iterations is None:
+            iterations = self.steps_done
+        return RunResult(self.steps_done, iterations, converged, last_norm, ev0.elapsed_time(ev1) / 1e3,
+                         launches, checks, cfg.nx, cfg.ny)
 
     def _run_resident(self, steps: int) -> RunResult:
         cfg = self.cfg

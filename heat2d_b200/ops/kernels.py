@@ -196,20 +196,26 @@ class Plan:
     def scratch_bytes(tile: N.Tile, kmax: int, chunk_rows: int = 0) -> int:
         return int(N.cuda().h2d_plan_scratch_bytes(C.byref(tile), kmax, chunk_rows))
 
-    def launch(self, src_parity: int, k: int, epoch: int, norm: str = "none"):
+    def launch(self, src_parity: int, k: int, epoch: int, norm: str = "none", ctl_ptr: int = 0,
+               run_if: int = 0):
+        """One k-step launch.  With `ctl_ptr` the launch is a device-side no-op
+        unless the word at ctl_ptr equals `run_if` (see h2d_plan_launch_ex)."""
         with torch.cuda.device(self.device):
-            N.check(self._lib, self._lib.h2d_plan_launch(self._h, src_parity, k, epoch & 0xFFFFFFFF,
-                                                         N.NORM[norm], _stream_ptr(self.device)))
+            N.check(self._lib, self._lib.h2d_plan_launch_ex(self._h, src_parity, k, epoch & 0xFFFFFFFF,
+                                                            N.NORM[norm], ctl_ptr or None, run_if & 0xFFFFFFFF,
+                                                            _stream_ptr(self.device)))
 
     @staticmethod
-    def run_many(plans, src_parity: int, k: int, n_launches: int, epoch0: int):
+    def run_many(plans, src_parity: int, k: int, n_launches: int, epoch0: int, ctl_ptrs=None):
         """`n_launches` back-to-back k-step launches of every plan in `plans` (one
-        native call: the per-launch cost is the bare cudaLaunchKernel)."""
+        native call: the per-launch cost is the bare cudaLaunchKernel).  `ctl_ptrs`
+        (one device word per plan) puts them under device-side run control."""
         lib = plans[0]._lib
         arr = (C.c_void_p * len(plans))(*[p._h for p in plans])
+        ctl = (C.c_void_p * len(plans))(*ctl_ptrs) if ctl_ptrs else None
         with torch.cuda.device(plans[0].device):
             N.check(lib, lib.h2d_plan_run_many(arr, len(plans), src_parity, k, n_launches,
-                                               epoch0 & 0xFFFFFFFF, _stream_ptr(plans[0].device)))
+                                               epoch0 & 0xFFFFFFFF, ctl, _stream_ptr(plans[0].device)))
 
     @property
     def launch_count(self) -> int:

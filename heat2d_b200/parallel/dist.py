@@ -196,16 +196,6 @@ class DistributedHeat2DSolver(Heat2DSolver):
         self.barrier()
         return self
 
-    def _launch_all(self, L: Launch, norm: str):
-        self.epoch += 1
-        self.engines[0].launch(self.parity, L.k, self.epoch, norm)
-
-    def _norm_value(self, norm: str) -> float:
-        self.norm_seq += 1
-        e = self.engines[0]
-        e.finish(self.norm_seq, norm, self.cfg.eps, 2)
-        return float(e.norm_total.item())
-
     def run(self, steps: Optional[int] = None) -> RunResult:
         self.barrier()
         res = super().run(steps)

@@ -197,6 +197,17 @@ void h2d_plan_destroy(h2d_plan_t* plan);
 int h2d_plan_launch(h2d_plan_t* plan, int src_parity, int k, uint32_t epoch, int norm,
                     void* stream);
 
+/* Same, under device-side run control: the launch is a no-op unless the device
+ * word *ctl equals run_if (ctl == NULL: unconditional).  With ctl = the word
+ * h2d_cuda_norm_finish sets on convergence and run_if = 0, everything queued
+ * after a converged check drains without doing work and WITHOUT the host ever
+ * synchronising inside the step loop (the reference stops with a host-side
+ * `break` after a blocking MPI_Allreduce, grad1612_mpi_heat.c:268-269).
+ * run_if = q (> 0) makes a launch that runs ONLY if check number q converged:
+ * used to regenerate the pre-step field the reference returns.               */
+int h2d_plan_launch_ex(h2d_plan_t* plan, int src_parity, int k, uint32_t epoch, int norm,
+                       const uint32_t* ctl, uint32_t run_if, void* stream);
+
 /* `n_launches` consecutive k-step launches without going back to the caller:
  * launch l uses epoch0 + l and alternates the source parity starting from
  * `src_parity`; with several plans (tiles emulated in one process) each launch
@@ -205,7 +216,7 @@ int h2d_plan_launch(h2d_plan_t* plan, int src_parity, int k, uint32_t epoch, int
  * cudaLaunchKernel (the reference pays one host launch per time step,
  * grad1612_cuda_heat.cu:82-85).                                               */
 int h2d_plan_run_many(h2d_plan_t* const* plans, int n_plans, int src_parity, int k, int n_launches,
-                      uint32_t epoch0, void* stream);
+                      uint32_t epoch0, const uint32_t* const* ctls /* per plan, or NULL */, void* stream);
 
 /* Number of kernels launched by this plan since creation (bench bookkeeping). */
 int64_t h2d_plan_launch_count(const h2d_plan_t* plan);
@@ -267,6 +278,12 @@ int h2d_cuda_norm_finish(const float* local_val, float* const* vals, uint32_t* c
                          int rank, int world, uint32_t seq, int norm, float eps,
                          float* out_dev, uint32_t* stop_dev, int phase /*0 publish,1 combine,2 both*/,
                          int64_t spin_timeout_ns, uint32_t* fault_dev, void* stream);
+/* Same with run control: does nothing if *ctl != 0 (an earlier check already
+ * stopped the run); on convergence stores `seq` into *ctl.                    */
+int h2d_cuda_norm_finish_ctl(const float* local_val, float* const* vals, uint32_t* const* flags,
+                             int rank, int world, uint32_t seq, int norm, float eps,
+                             float* out_dev, uint32_t* ctl, int phase, int64_t spin_timeout_ns,
+                             uint32_t* fault_dev, void* stream);
 
 /* ---- halo pack / unpack for the NCCL-halo BASELINE backend (K8) ----------- */
 /* Pack the owned edge (width w) facing direction dir (N,S,W,E) into `out`

@@ -11,14 +11,12 @@ def test_plain_schedule():
     assert make_schedule(0, 8) == []
 
 
-def test_exact_conv_schedule_checks_on_multiples_of_interval():
-    s = make_schedule(100, 8, conv=True, interval=20, conv_mode="exact")
-    assert sum(l.k for l in s) == 100
-    checks = [l for l in s if l.check]
-    assert [l.first_step for l in checks] == [0, 20, 40, 60, 80]
-    assert all(l.k == 1 for l in checks)
+def test_conv_schedule_is_the_same_for_both_modes():
+    a = make_schedule(100, 8, conv=True, interval=20, conv_mode="exact")
+    b = make_schedule(100, 8, conv=True, interval=20, conv_mode="fused-k")
+    assert a == b
     pos = 0
-    for l in s:
+    for l in a:
         assert l.first_step == pos
         pos += l.k
 
@@ -33,7 +31,7 @@ def test_fused_conv_schedule_ends_launch_on_checked_step():
 
 def test_schedule_with_start_step():
     s = make_schedule(50, 8, conv=True, interval=20, conv_mode="exact", start_step=30)
-    assert [l.first_step for l in s if l.check] == [40, 60]
+    assert [l.first_step + l.k - 1 for l in s if l.check] == [40, 60]
     assert sum(l.k for l in s) == 50
 
 

@@ -28,24 +28,27 @@ def time_cfg(cfg, reps=3):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--n", type=int, default=16384)
+    ap.add_argument("--nx", type=int, default=0)
+    ap.add_argument("--ny", type=int, default=0)
     ap.add_argument("--steps", type=int, default=64)
     ap.add_argument("--ks", default="1,2,4,6,8")
     ap.add_argument("--chunks", default="0")
     ap.add_argument("--arith", default="fp32")
     ap.add_argument("--plain", action="store_true")
     a = ap.parse_args()
+    nx, ny = (a.nx or a.n), (a.ny or a.n)
     out = []
     if a.plain:
-        g = time_cfg(HeatConfig(nx=a.n, ny=a.n, steps=16, backend="plain", k=1, arith=a.arith))
+        g = time_cfg(HeatConfig(nx=nx, ny=ny, steps=16, backend="plain", k=1, arith=a.arith))
         out.append({"kernel": "plain_k1", "glups": g})
         print(out[-1], flush=True)
     for k in map(int, a.ks.split(",")):
         for ch in map(int, a.chunks.split(",")):
-            g = time_cfg(HeatConfig(nx=a.n, ny=a.n, steps=a.steps, k=k, chunk_rows=ch, arith=a.arith))
-            out.append({"kernel": f"tk_k{k}", "chunk_rows": ch, "arith": a.arith, "n": a.n, "glups": g})
+            g = time_cfg(HeatConfig(nx=nx, ny=ny, steps=a.steps, k=k, chunk_rows=ch, arith=a.arith))
+            out.append({"kernel": f"tk_k{k}", "chunk_rows": ch, "arith": a.arith, "n": [nx, ny], "glups": g})
             print(out[-1], flush=True)
     os.makedirs("gpurun_out", exist_ok=True)
-    with open(f"gpurun_out/probe_{a.arith}_{a.n}.json", "w") as f:
+    with open(f"gpurun_out/probe_{a.arith}_{nx}x{ny}.json", "w") as f:
         json.dump(out, f, indent=1)
 
 
