@@ -356,9 +356,10 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
     const bool frozen = (g.x0 + r_lo - K < g.ax_lo) || (g.x0 + r_hi - 1 + K > g.ax_hi) ||
                         (g.y0 + jb < g.ay_lo) || (g.y0 + jb + TK_W - 1 > g.ay_hi);
     const bool extras = comm_edge || a.norm != H2D_NORM_NONE;
-    if (extras) {
-      // Cold variants: one instantiation handles frozen and active footprints.
+    if (extras && frozen) {
       acc = run_task<K, ARITH, IMM, true, true>(&tmap, a, strip, chunk, comm_edge, ring, bars, lane);
+    } else if (extras) {
+      acc = run_task<K, ARITH, IMM, false, true>(&tmap, a, strip, chunk, comm_edge, ring, bars, lane);
     } else if (frozen) {
       acc = run_task<K, ARITH, IMM, true, false>(&tmap, a, strip, chunk, false, ring, bars, lane);
     } else {

@@ -148,10 +148,12 @@ def make_schedule(steps: int, k: int, conv: bool = False, interval: int = 20,
             s += kk
             continue
         n = nxt - s + 1  # steps up to and including the checked one: the last launch ends on it
-        while n > k:
-            out.append(Launch(k, False, s))
-            s += k
-            n -= k
-        out.append(Launch(n, True, s))
-        s += n
+        # as few launches as k allows, of (nearly) equal depth: 20 steps at k = 8 -> 7 + 7 + 6,
+        # not 8 + 8 + 4 (a shallow launch is HBM-bound, a deep one is not)
+        parts = -(-n // k)
+        base, extra = divmod(n, parts)
+        for i in range(parts):
+            kk = base + (1 if i < extra else 0)
+            out.append(Launch(kk, i == parts - 1, s))
+            s += kk
     return out
