@@ -17,8 +17,10 @@ __device__ __forceinline__ float init_value_dev(int32_t nx, int32_t ny, int32_t 
   if (mode == H2D_INIT_ZERO) return 0.0f;
   if (x < 0 || x >= nx || y < 0 || y >= ny) return 0.0f;
   if (mode == H2D_INIT_EXACT) {
-    long long p = (long long)x * (long long)(nx - x - 1) * (long long)y * (long long)(ny - y - 1);
-    return __ll2float_rn(p);
+    const long long a = (long long)x * (long long)(nx - x - 1);
+    const long long b = (long long)y * (long long)(ny - y - 1);
+    if (h2d_exact_fits_int64(nx, ny)) return __ll2float_rn(a * b);
+    return __double2float_rn(__dmul_rn((double)a, (double)b));  // same rounding as the oracle
   }
   unsigned p = (unsigned)x * (unsigned)(nx - x - 1);
   p *= (unsigned)y;

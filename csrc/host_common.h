@@ -33,6 +33,15 @@ inline int h2d_check_tile(const h2d_tile_t* t) {
   return H2D_OK;
 }
 
+// x(nx-x-1) y(ny-y-1) peaks at (nx/2)^2 (ny/2)^2: does it fit a signed 64-bit integer?
+#ifdef __CUDACC__
+__host__ __device__
+#endif
+inline bool h2d_exact_fits_int64(int32_t nx, int32_t ny) {
+  const double peak = 0.25 * (double)nx * (double)nx * 0.25 * (double)ny * (double)ny;
+  return peak < 4.0e18;
+}
+
 // Value of the initial condition at global (x, y); defined in oracle.cpp and
 // duplicated (device) in init.cu.
 float h2d_init_value(int32_t nx, int32_t ny, int32_t x, int32_t y, int mode);

@@ -139,9 +139,13 @@ float h2d_init_value(int32_t nx, int32_t ny, int32_t x, int32_t y, int mode) {
   if (mode == H2D_INIT_ZERO) return 0.0f;
   if (x < 0 || x >= nx || y < 0 || y >= ny) return 0.0f;
   if (mode == H2D_INIT_EXACT) {
-    // int64 is enough up to 65536^2 (peak 1.15e18 < 2^63), SURVEY 7.3.
-    int64_t p = (int64_t)x * (int64_t)(nx - x - 1) * (int64_t)y * (int64_t)(ny - y - 1);
-    return (float)p;
+    // int64 is enough up to 65536^2 (peak 1.15e18 < 2^63), SURVEY 7.3.  Beyond that
+    // (weak scaling to 131072 x 262144) the two factors, each exact below 2^53, are
+    // multiplied in double: one extra rounding, identical on CPU and GPU.
+    const int64_t a = (int64_t)x * (int64_t)(nx - x - 1);
+    const int64_t b = (int64_t)y * (int64_t)(ny - y - 1);
+    if (h2d_exact_fits_int64(nx, ny)) return (float)(a * b);
+    return (float)((double)a * (double)b);
   }
   // ((x*(nx-x-1))*y)*(ny-y-1), left to right in 32 bits (mpi_heat2Dn.c:247).
   uint32_t p = (uint32_t)x * (uint32_t)(nx - x - 1);
