@@ -53,7 +53,26 @@ void run(const char* name, int ops_per_inner, int warps_per_smsp) {
   cudaFree(out); cudaFree(cyc);
 }
 
+// Whole-chip fp32 rate with the packed immediate form (the kernels' hot instruction), event-timed.
+static void peak() {
+  float* out; long long* cyc;
+  const int threads = 512, blocks = 148 * 4;
+  cudaMalloc(&out, (size_t)blocks * threads * sizeof(float));
+  cudaMalloc(&cyc, 8 * 2 * 64);
+  cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+  for (int rep = 0; rep < 3; ++rep) {
+    cudaEventRecord(e0);
+    for (int i = 0; i < 20; ++i) k<1><<<blocks, threads>>>(out, 0.999f, 0.001f, cyc);
+    cudaEventRecord(e1); cudaEventSynchronize(e1);
+  }
+  float ms; cudaEventElapsedTime(&ms, e0, e1);
+  const double fma = 20.0 * blocks * threads * (double)ITERS * 8 * 2;  // FFMA2 = 2 FMA per lane
+  printf("PEAK fp32 (FFMA2 imm, whole chip, event-timed): %.1f TFLOP/s  (%.3f ms for %.3e FMA)\n",
+         2.0 * fma / (ms * 1e-3) / 1e12, ms, fma);
+}
+
 int main() {
+  peak();
   for (int w : {1, 3, 4, 8}) {
     if (w == 1) printf("--- latency-ish (1 warp per SMSP, 8 chains)\n"); else printf("--- %d warps per SMSP\n", w);
     switch (w) { default: break; }
