@@ -24,6 +24,7 @@
 // (up, centre) in registers, so the state is 2*4*K floats per lane.
 #include <cuda.h>
 #include <cstdio>
+#include <cstdlib>
 #include <cmath>
 #include <cstring>
 #include <type_traits>
@@ -69,6 +70,7 @@ struct TkArgs {
   // convergence check stopped the run (set by norm_finish_kernel).
   const uint32_t* ctl;
   uint32_t run_if;
+  int32_t debug;   // bit 0: skip the peer stores (timing experiments only; H2D_DEBUG_NOFWD=1)
 };
 
 // ------------------------------------------------------------ PTX wrappers
@@ -133,7 +135,7 @@ __device__ __noinline__ void forward_row(const TkArgs& a, int rho, int j0, float
       const bool in = (sy == 0) || (sy < 0 ? j < fw : j >= a.g.cols - fw);
       if (in && ((smask >> e) & 1)) m |= 1 << e;
     }
-    if (m == 0) continue;
+    if (m == 0 || (a.debug & 1)) continue;
     float* q = p.buf + (int64_t)(a.g.x0 + rho - p.x0 + p.halo_r) * p.pitch +
                (a.g.y0 + j0 - p.y0 + p.halo_c);
     if (m == 15 && (((uintptr_t)q) & 15) == 0) {
@@ -743,6 +745,11 @@ int h2d_plan_launch_ex(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int
   a.timeout_ns = p->desc.spin_timeout_ns > 0 ? p->desc.spin_timeout_ns : 10000000000LL;
   a.ctl = ctl;
   a.run_if = run_if;
+  {
+    static int dbg = -1;
+    if (dbg < 0) { const char* e = getenv("H2D_DEBUG_NOFWD"); dbg = (e && e[0] == '1') ? 1 : 0; }
+    a.debug = dbg;
+  }
 
   const int grid = (tl.n_tasks + TK_WARPS - 1) / TK_WARPS;
   fn<<<grid, TK_WARPS * 32, TK_SMEM_BYTES, (cudaStream_t)stream>>>(p->tmap[src_parity], a);

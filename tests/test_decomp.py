@@ -59,5 +59,7 @@ def test_strips_and_auto():
     assert [(t.x0, t.rows) for t in d.tiles] == [(0, 214), (214, 213), (427, 213)]
     assert all(t.cols == 640 for t in d.tiles)
     a = Decomposition.auto(32768, 32768, 8)
-    assert a.px * a.py == 8
+    assert (a.px, a.py) == (8, 1)          # row strips on an NVSwitch box
+    b = Decomposition.auto(640, 65536, 8)  # too few rows for 8 strips of >= 512
+    assert b.px * b.py == 8 and b.py > 1
     assert Decomposition.auto(100, 100, 1).world == 1
