@@ -19,6 +19,12 @@ namespace h2d {
 constexpr int RES_THREADS = 1024;
 constexpr int RES_MAX_SMEM = 227 * 1024;
 
+// Shared-memory layout of one CTA: two buffers of (band + 2) rows x nyp floats;
+// owned column j lives at float RES_LPAD + j of a row, so 4-column groups are
+// 16-byte aligned; RES_LPAD floats of zeros on the left, >= 4 on the right.
+constexpr int RES_LPAD = 4;
+__host__ __device__ inline int res_pitch(int ny) { return ((ny + 3) & ~3) + 2 * RES_LPAD; }
+
 template <int ARITH>
 __global__ void __launch_bounds__(RES_THREADS, 1)
 resident_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t pitch,
@@ -28,7 +34,7 @@ resident_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t 
   const int nblk = (int)cluster.num_blocks();
   extern __shared__ __align__(16) float sm[];
   const int nx = g.nx, ny = g.ny;
-  const int nyp = ny + 2;
+  const int nyp = res_pitch(ny);
   const int bstride = (band + 2) * nyp;
   float* buf0 = sm;
   float* buf1 = sm + bstride;
@@ -45,7 +51,7 @@ resident_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t 
     const int gx = x_lo + r - 1;
     if (gx < 0 || gx >= nx) continue;
     const float* s = src + (int64_t)gx * pitch;
-    for (int j = lane; j < ny; j += 32) buf0[r * nyp + 1 + j] = s[j];
+    for (int j = lane; j < ny; j += 32) buf0[r * nyp + RES_LPAD + j] = s[j];
   }
   __syncthreads();
 
@@ -63,31 +69,45 @@ resident_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t 
   }
   cluster.sync();
 
+  // Work items: (owned row, group of 4 columns), strided over the 1024 threads;
+  // one LDS.128 each for the rows above / at / below, two scalar loads for the
+  // horizontal neighbours outside the group, packed fp32 math, one STS.128.
+  const int groups = (ny + 3) >> 2;
+  const int n_items = my_rows * groups;
   int cur = 0;
   for (int64_t s = 0; s < steps; ++s) {
-    for (int r = 1 + warp; r <= my_rows; r += NW) {
-      const int gx = x_lo + r - 1;
+    for (int it = threadIdx.x; it < n_items; it += RES_THREADS) {
+      const int r = it / groups;            // 0-based owned row
+      const int gq = it - r * groups;       // group index
+      const int j = gq << 2;                // first column of the group
+      const int gx = x_lo + r;
+      const float* c = A + (r + 1) * nyp + RES_LPAD + j;
+      const float4 cv = *reinterpret_cast<const float4*>(c);
+      const float4 uv = *reinterpret_cast<const float4*>(c - nyp);
+      const float4 dv = *reinterpret_cast<const float4*>(c + nyp);
+      const float L = c[-1], R = c[4];
+      float4 o = point4<ARITH>(uv, cv, dv, L, R, g);
       const bool ract = gx >= g.ax_lo && gx <= g.ax_hi;
-      const float* c = A + r * nyp + 1;
-      float* o = B + r * nyp + 1;
-      for (int j = lane; j < ny; j += 32) {
-        const float cv = c[j];
-        float v = cv;
-        if (ract && j >= g.ay_lo && j <= g.ay_hi)
-          v = point<ARITH>(cv, c[j - nyp], c[j + nyp], c[j - 1], c[j + 1], g);
-        o[j] = v;
-      }
+      o.x = (ract && j + 0 >= g.ay_lo && j + 0 <= g.ay_hi) ? o.x : cv.x;
+      o.y = (ract && j + 1 >= g.ay_lo && j + 1 <= g.ay_hi) ? o.y : cv.y;
+      o.z = (ract && j + 2 >= g.ay_lo && j + 2 <= g.ay_hi) ? o.z : cv.z;
+      o.w = (ract && j + 3 >= g.ay_lo && j + 3 <= g.ay_hi) ? o.w : cv.w;
+      // columns >= ny (padding of a partial last group) are inactive: they copy zeros
+      *reinterpret_cast<float4*>(B + (r + 1) * nyp + RES_LPAD + j) = o;
     }
     __syncthreads();
-    // Push my edge rows of the new field into the neighbours' ghost rows.
+    // Push my edge rows of the new field into the neighbours' ghost rows (DSMEM).
     const int nb = cur ^ 1;
+    const int n4 = nyp >> 2;
     if (up_ghost[nb] != nullptr) {
-      const float* row = B + 1 * nyp;
-      for (int j = threadIdx.x; j < nyp; j += RES_THREADS) up_ghost[nb][j] = row[j];
+      const float4* row = reinterpret_cast<const float4*>(B + 1 * nyp);
+      float4* dstp = reinterpret_cast<float4*>(up_ghost[nb]);
+      for (int j = threadIdx.x; j < n4; j += RES_THREADS) dstp[j] = row[j];
     }
     if (dn_ghost[nb] != nullptr) {
-      const float* row = B + my_rows * nyp;
-      for (int j = threadIdx.x; j < nyp; j += RES_THREADS) dn_ghost[nb][j] = row[j];
+      const float4* row = reinterpret_cast<const float4*>(B + my_rows * nyp);
+      float4* dstp = reinterpret_cast<float4*>(dn_ghost[nb]);
+      for (int j = threadIdx.x; j < n4; j += RES_THREADS) dstp[j] = row[j];
     }
     cluster.sync();
     float* t = A; A = B; B = t;
@@ -97,7 +117,7 @@ resident_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t 
   for (int r = 1 + warp; r <= my_rows; r += NW) {
     const int gx = x_lo + r - 1;
     float* d = dst + (int64_t)gx * pitch;
-    const float* c = A + r * nyp + 1;
+    const float* c = A + r * nyp + RES_LPAD;
     for (int j = lane; j < ny; j += 32) d[j] = c[j];
   }
 }
@@ -116,7 +136,7 @@ static bool resident_shape(int nx, int ny, int max_cluster, ResidentShape* out) 
       const int band = (nx + n - 1) / n;
       if ((n - 1) * band >= nx) continue;               // last CTA would own nothing
       if (pass == 0 && n > 1 && band < 8) continue;      // preference only
-      const size_t smem = (size_t)2 * (band + 2) * (ny + 2) * sizeof(float);
+      const size_t smem = (size_t)2 * (band + 2) * res_pitch(ny) * sizeof(float);
       if (smem > (size_t)RES_MAX_SMEM) break;            // fewer CTAs only need more
       out->ncta = n; out->band = band; out->smem = smem;
       return true;
