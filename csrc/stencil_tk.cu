@@ -38,7 +38,11 @@ constexpr int TK_BR = 6;       // rows per TMA box (a multiple of the 3-row regi
 constexpr int TK_STAGES = 4;   // boxes in flight per warp
 constexpr int TK_WARPS = 4;    // warps (tasks) per CTA
 constexpr int TK_STAGE_BYTES = TK_BR * TK_W * 4;
-constexpr int TK_SMEM_BYTES = TK_WARPS * TK_STAGES * TK_STAGE_BYTES + TK_WARPS * TK_STAGES * 8;
+constexpr int TK_WE_ROWS = 16;   // rows of column-halo data staged per remote store
+constexpr int TK_WE_BYTES = 2 * TK_WE_ROWS * 8 * 4;   // per warp: W and E side, 8 floats per row
+constexpr int TK_SMEM_RING = TK_WARPS * TK_STAGES * TK_STAGE_BYTES;
+constexpr int TK_SMEM_BARS = TK_WARPS * TK_STAGES * 8;
+constexpr int TK_SMEM_BYTES = TK_SMEM_RING + TK_SMEM_BARS + TK_WARPS * TK_WE_BYTES;
 constexpr int TK_KMAX = 8;
 
 struct PeerDev {
@@ -115,7 +119,8 @@ __device__ __forceinline__ float4 lds128(uint32_t addr) {
 // Store the 4 just-computed values of owned row `rho`, columns j0..j0+3, into
 // every neighbour whose ghost margin contains them.  Called only by tasks that
 // touch the tile edge.  `smask` = which of the 4 elements are owned outputs.
-__device__ __noinline__ void forward_row(const TkArgs& a, int rho, int j0, float4 o, int smask) {
+__device__ __noinline__ void forward_row(const TkArgs& a, int rho, int j0, float4 o, int smask,
+                                         bool skip_we) {
   const int fw = a.fw;
   const float v[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll 1
@@ -126,6 +131,7 @@ __device__ __noinline__ void forward_row(const TkArgs& a, int rho, int j0, float
                  : (d == H2D_S || d == H2D_SW || d == H2D_SE) ? 1 : 0;
     const int sy = (d == H2D_W || d == H2D_NW || d == H2D_SW) ? -1
                  : (d == H2D_E || d == H2D_NE || d == H2D_SE) ? 1 : 0;
+    if (sx == 0 && skip_we) continue;   // pure W / E: batched by flush_we()
     if (sx < 0 && rho >= fw) continue;
     if (sx > 0 && rho < a.g.rows - fw) continue;
     int m = 0;
@@ -148,6 +154,33 @@ __device__ __noinline__ void forward_row(const TkArgs& a, int rho, int j0, float
   }
 }
 
+// Column halos, batched.  A remote store stalls the issuing warp for about an
+// NVLink round trip, and a column halo is only 32 bytes per row: storing it row
+// by row made a 1x2 split 16 % slower than a 2x1 split (6770 vs 8052 GLUP/s on
+// two B200).  Instead the two float4 per row and side are parked in shared
+// memory and every TK_WE_ROWS rows the whole warp issues ONE store instruction:
+// lane l sends row l/2, half l%2 (16 rows x 32 bytes).  `own` = which halves
+// (bit 0/1: W, bit 2/3: E) this warp's lanes hold.
+__device__ __noinline__ void flush_we(const TkArgs& a, uint32_t stage, int rho0, int count, int own,
+                                      int lane) {
+  __syncwarp();
+  const int row = lane >> 1, half = lane & 1;
+  if (row < count) {
+#pragma unroll
+    for (int side = 0; side < 2; ++side) {
+      if (!((own >> (2 * side + half)) & 1)) continue;
+      const PeerDev& p = a.peer[side == 0 ? H2D_W : H2D_E];
+      if (p.buf == nullptr) continue;
+      const float4 v = lds128(stage + (uint32_t)(((side * TK_WE_ROWS + row) * 2 + half) * 16));
+      const int jcol = (side == 0 ? 0 : a.g.cols - 8) + half * 4;   // tile-local first column
+      float* q = p.buf + (int64_t)(a.g.x0 + rho0 + row - p.x0 + p.halo_r) * p.pitch +
+                 (a.g.y0 + jcol - p.y0 + p.halo_c);
+      *reinterpret_cast<float4*>(q) = v;
+    }
+  }
+  __syncwarp();
+}
+
 // ------------------------------------------------------------- one task
 // FROZEN: the footprint contains cells that keep their value (global boundary
 // or outside the grid) -> per-element select.  EXTRAS: the task forwards rows
@@ -157,7 +190,7 @@ __device__ __noinline__ void forward_row(const TkArgs& a, int rho, int j0, float
 template <int K, int ARITH, bool IMM, bool FROZEN, bool EXTRAS>
 __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs& a, int strip,
                                           int chunk, bool comm_edge, uint32_t ring,
-                                          uint32_t bars, int lane) {
+                                          uint32_t bars, uint32_t we_stage, int lane) {
   const Geo& g = a.g;
   const int R = a.chunk_rows;
   const int r_lo = chunk * R;
@@ -183,6 +216,27 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
     if (lane_in && (j0 + e) >= 0 && (j0 + e) < g.cols) smask |= 1 << e;
   const bool st_full = smask == 15;
   const bool st_part = smask != 0 && smask != 15;
+
+  // Batched column halos (EXTRAS only): usable when the 8-column bands are whole
+  // float4s of single lanes.  we_half: 0/1 = my float4 is half 0/1 of the W band,
+  // 2/3 = of the E band, -1 = not in a band.
+  int we_half = -1, we_own = 0, we_count = 0, we_rho0 = 0;
+  bool we_batched = false;
+  if (EXTRAS) {
+    we_batched = comm_edge && a.fw == 8 && (g.cols & 3) == 0 && g.cols >= 16 &&
+                 (a.peer[H2D_W].buf != nullptr || a.peer[H2D_E].buf != nullptr);
+    if (we_batched && smask == 15) {
+      if (a.peer[H2D_W].buf != nullptr && (j0 == 0 || j0 == 4)) we_half = j0 >> 2;
+      if (a.peer[H2D_E].buf != nullptr && (j0 == g.cols - 8 || j0 == g.cols - 4))
+        we_half = 2 + ((j0 - (g.cols - 8)) >> 2);
+    }
+    if (we_batched) {
+#pragma unroll
+      for (int h = 0; h < 4; ++h)
+        if (__ballot_sync(0xffffffffu, we_half == h) != 0u) we_own |= 1 << h;
+      if (we_own == 0) we_batched = false;   // this strip holds no band column
+    }
+  }
 
   bool act[4] = {true, true, true, true};
   if (FROZEN) {
@@ -258,7 +312,7 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
         if (smask & 8) q[3] = fin.w;
       }
       if (EXTRAS && smask != 0) {
-        if (comm_edge) forward_row(a, r_lo + ro, j0, fin, smask);
+        if (comm_edge) forward_row(a, r_lo + ro, j0, fin, smask, we_batched);
         if (a.norm != H2D_NORM_NONE) {
           const float d0 = (smask & 1) ? fin.x - cprev.x : 0.f;
           const float d1 = (smask & 2) ? fin.y - cprev.y : 0.f;
@@ -271,6 +325,19 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
             acc = fmaxf(acc, fmaxf(fmaxf(fabsf(d0), fabsf(d1)), fmaxf(fabsf(d2), fabsf(d3))));
           }
         }
+      }
+    }
+    if (EXTRAS && we_batched && (unsigned)ro < (unsigned)n_out) {
+      if (we_count == 0) we_rho0 = r_lo + ro;
+      if (we_half >= 0) {
+        const uint32_t slot = we_stage + (uint32_t)((((we_half >> 1) * TK_WE_ROWS + we_count) * 2 + (we_half & 1)) * 16);
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(slot), "f"(fin.x), "f"(fin.y),
+                     "f"(fin.z), "f"(fin.w) : "memory");
+      }
+      ++we_count;
+      if (we_count == TK_WE_ROWS || ro == n_out - 1) {
+        flush_we(a, we_stage, we_rho0, we_count, we_own, lane);
+        we_count = 0;
       }
     }
     q += g.pitch;
@@ -321,7 +388,8 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int task = (int)blockIdx.x * TK_WARPS + warp;
   const uint32_t ring = smem_u32(smem) + warp * (TK_STAGES * TK_STAGE_BYTES);
-  const uint32_t bars = smem_u32(smem) + TK_WARPS * TK_STAGES * TK_STAGE_BYTES + warp * TK_STAGES * 8;
+  const uint32_t bars = smem_u32(smem) + TK_SMEM_RING + warp * TK_STAGES * 8;
+  const uint32_t we_stage = smem_u32(smem) + TK_SMEM_RING + TK_SMEM_BARS + warp * TK_WE_BYTES;
 
   float acc = 0.f;
   if (task < a.n_tasks) {
@@ -359,13 +427,13 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
                         (g.y0 + jb < g.ay_lo) || (g.y0 + jb + TK_W - 1 > g.ay_hi);
     const bool extras = comm_edge || a.norm != H2D_NORM_NONE;
     if (extras && frozen) {
-      acc = run_task<K, ARITH, IMM, true, true>(&tmap, a, strip, chunk, comm_edge, ring, bars, lane);
+      acc = run_task<K, ARITH, IMM, true, true>(&tmap, a, strip, chunk, comm_edge, ring, bars, we_stage, lane);
     } else if (extras) {
-      acc = run_task<K, ARITH, IMM, false, true>(&tmap, a, strip, chunk, comm_edge, ring, bars, lane);
+      acc = run_task<K, ARITH, IMM, false, true>(&tmap, a, strip, chunk, comm_edge, ring, bars, we_stage, lane);
     } else if (frozen) {
-      acc = run_task<K, ARITH, IMM, true, false>(&tmap, a, strip, chunk, false, ring, bars, lane);
+      acc = run_task<K, ARITH, IMM, true, false>(&tmap, a, strip, chunk, false, ring, bars, we_stage, lane);
     } else {
-      acc = run_task<K, ARITH, IMM, false, false>(&tmap, a, strip, chunk, false, ring, bars, lane);
+      acc = run_task<K, ARITH, IMM, false, false>(&tmap, a, strip, chunk, false, ring, bars, we_stage, lane);
     }
 
     if (comm_edge) {
