@@ -75,6 +75,7 @@ struct TkArgs {
   const uint32_t* ctl;
   uint32_t run_if;
   int32_t debug;   // bit 0: skip the peer stores (timing experiments only; H2D_DEBUG_NOFWD=1)
+                   // bit 1: random per-task delays around the flag protocol (H2D_DEBUG_DELAY=1)
 };
 
 // ------------------------------------------------------------ PTX wrappers
@@ -404,6 +405,13 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
     const bool comm_edge = (tk.x < 0) && a.has_peers;
     const int chunk = tk.y;
 
+    if (comm_edge && (a.debug & 2)) {
+      // Stress mode (race detection): shake the order in which ranks reach
+      // the flag protocol with a pseudo-random delay of up to ~64 us per edge task.
+      const uint32_t h = ((uint32_t)task * 2654435761u) ^ (a.epoch * 40503u) ^ ((uint32_t)a.g.x0 * 97u + (uint32_t)a.g.y0);
+      const uint64_t t0 = globaltimer_ns();
+      while (globaltimer_ns() - t0 < (uint64_t)((h >> 7) & 0xffffu)) __nanosleep(256);
+    }
     if (comm_edge) {
       // Ghost cells of src were written by the neighbours' launch `epoch-1`;
       // their ghost cells of OUR dst parity were last read by that launch too.
@@ -815,7 +823,11 @@ int h2d_plan_launch_ex(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int
   a.run_if = run_if;
   {
     static int dbg = -1;
-    if (dbg < 0) { const char* e = getenv("H2D_DEBUG_NOFWD"); dbg = (e && e[0] == '1') ? 1 : 0; }
+    if (dbg < 0) {
+      const char* e = getenv("H2D_DEBUG_NOFWD");
+      const char* d = getenv("H2D_DEBUG_DELAY");
+      dbg = ((e && e[0] == '1') ? 1 : 0) | ((d && d[0] == '1') ? 2 : 0);
+    }
     a.debug = dbg;
   }
 

@@ -28,11 +28,14 @@ def _free_port():
     return p
 
 
-def _run(nproc, spec, timeout=600):
+def _run(nproc, spec, timeout=600, env_extra=None):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
            os.path.join(HERE, "_dist_gpu_worker.py"), json.dumps(spec)]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout)
+    env = dict(os.environ)
+    if env_extra:
+        env.update(env_extra)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
     return json.loads(line)
@@ -67,4 +70,18 @@ def test_four_gpus():
 @pytest.mark.skipif(_ngpu() < 8, reason="needs 8 GPUs")
 def test_eight_gpus():
     out = _run(8, {"cases": _cases(2, 4)})
+    assert out["ok"], out
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+def test_flag_protocol_under_injected_delays():
+    """Race detection for the fused halo exchange: every edge task sleeps a pseudo-random
+    time (up to ~64 us) before it touches the flag protocol, on every rank differently;
+    the result must still be bit-identical to the oracle (a missing RAW/WAR edge in the
+    protocol shows up as a mismatch)."""
+    n = min(_ngpu(), 4)
+    px, py = (2, 2) if n >= 4 else (1, 2)
+    cases = [{"name": "delay", "random": True,
+              "cfg": dict(nx=768, ny=1024, px=px, py=py, k=8, steps=120, backend="fused", chunk_rows=32)}]
+    out = _run(px * py, {"cases": cases}, env_extra={"H2D_DEBUG_DELAY": "1"})
     assert out["ok"], out
