@@ -39,7 +39,9 @@ constexpr int TK_STAGES = 4;   // boxes in flight per warp
 constexpr int TK_WARPS = 4;    // warps (tasks) per CTA
 constexpr int TK_STAGE_BYTES = TK_BR * TK_W * 4;
 constexpr int TK_WE_ROWS = 16;   // rows of column-halo data staged per remote store
-constexpr int TK_WE_BYTES = 2 * TK_WE_ROWS * 8 * 4;   // per warp: W and E side, 8 floats per row
+constexpr int TK_WE_COLS = 32;   // columns forwarded per row and side: one full 128-byte line
+constexpr int TK_WE_Q = TK_WE_COLS / 4;               // float4 pieces per row and side
+constexpr int TK_WE_BYTES = 2 * TK_WE_ROWS * TK_WE_COLS * 4;   // per warp: W and E side
 constexpr int TK_SMEM_RING = TK_WARPS * TK_STAGES * TK_STAGE_BYTES;
 constexpr int TK_SMEM_BARS = TK_WARPS * TK_STAGES * 8;
 constexpr int TK_SMEM_BYTES = TK_SMEM_RING + TK_SMEM_BARS + TK_WARPS * TK_WE_BYTES;
@@ -155,25 +157,29 @@ __device__ __noinline__ void forward_row(const TkArgs& a, int rho, int j0, float
   }
 }
 
-// Column halos, batched.  A remote store stalls the issuing warp for about an
-// NVLink round trip, and a column halo is only 32 bytes per row: storing it row
-// by row made a 1x2 split 16 % slower than a 2x1 split (6770 vs 8052 GLUP/s on
-// two B200).  Instead the two float4 per row and side are parked in shared
-// memory and every TK_WE_ROWS rows the whole warp issues ONE store instruction:
-// lane l sends row l/2, half l%2 (16 rows x 32 bytes).  `own` = which halves
-// (bit 0/1: W, bit 2/3: E) this warp's lanes hold.
+// Column halos, batched and line-sized.  A column halo is only k floats per row,
+// and 32-byte remote stores are expensive twice over: they stall the issuing warp
+// for about an NVLink round trip each, and a partial-line write costs the
+// destination a read-modify-write (1x2 split: 6770 GLUP/s row by row, 7060 with 16
+// rows per store instruction, vs 8052 for the 2x1 split on two B200).  So each
+// row forwards a whole 128-byte line — the 32 edge columns, which is exactly the
+// neighbour's 32-column margin — parked in shared memory and sent every
+// TK_WE_ROWS rows: lane l sends pieces l and l+32 of the 16 x 8 float4 block.
+// `own` = which of the 8 pieces per side (bits 0-7: W, 8-15: E) this warp holds.
 __device__ __noinline__ void flush_we(const TkArgs& a, uint32_t stage, int rho0, int count, int own,
                                       int lane) {
   __syncwarp();
-  const int row = lane >> 1, half = lane & 1;
-  if (row < count) {
 #pragma unroll
-    for (int side = 0; side < 2; ++side) {
-      if (!((own >> (2 * side + half)) & 1)) continue;
-      const PeerDev& p = a.peer[side == 0 ? H2D_W : H2D_E];
-      if (p.buf == nullptr) continue;
-      const float4 v = lds128(stage + (uint32_t)(((side * TK_WE_ROWS + row) * 2 + half) * 16));
-      const int jcol = (side == 0 ? 0 : a.g.cols - 8) + half * 4;   // tile-local first column
+  for (int side = 0; side < 2; ++side) {
+    const PeerDev& p = a.peer[side == 0 ? H2D_W : H2D_E];
+    if (p.buf == nullptr || ((own >> (8 * side)) & 0xff) == 0) continue;
+#pragma unroll
+    for (int it = 0; it < (TK_WE_ROWS * TK_WE_Q) / 32; ++it) {
+      const int idx = it * 32 + lane;
+      const int row = idx / TK_WE_Q, piece = idx % TK_WE_Q;
+      if (row >= count || !((own >> (8 * side + piece)) & 1)) continue;
+      const float4 v = lds128(stage + (uint32_t)(((side * TK_WE_ROWS + row) * TK_WE_Q + piece) * 16));
+      const int jcol = (side == 0 ? 0 : a.g.cols - TK_WE_COLS) + piece * 4;   // tile-local column
       float* q = p.buf + (int64_t)(a.g.x0 + rho0 + row - p.x0 + p.halo_r) * p.pitch +
                  (a.g.y0 + jcol - p.y0 + p.halo_c);
       *reinterpret_cast<float4*>(q) = v;
@@ -218,23 +224,24 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
   const bool st_full = smask == 15;
   const bool st_part = smask != 0 && smask != 15;
 
-  // Batched column halos (EXTRAS only): usable when the 8-column bands are whole
-  // float4s of single lanes.  we_half: 0/1 = my float4 is half 0/1 of the W band,
-  // 2/3 = of the E band, -1 = not in a band.
-  int we_half = -1, we_own = 0, we_count = 0, we_rho0 = 0;
+  // Batched column halos (EXTRAS only): usable when the 32-column bands are whole
+  // float4s of single lanes and fit the neighbour's margin.  we_piece: 0..7 = my
+  // float4 is that piece of the W band, 8..15 = of the E band, -1 = not in a band.
+  int we_piece = -1, we_own = 0, we_count = 0, we_rho0 = 0;
   bool we_batched = false;
   if (EXTRAS) {
-    we_batched = comm_edge && a.fw == 8 && (g.cols & 3) == 0 && g.cols >= 16 &&
-                 (a.peer[H2D_W].buf != nullptr || a.peer[H2D_E].buf != nullptr);
+    const bool w_ok = a.peer[H2D_W].buf != nullptr && a.peer[H2D_W].halo_c >= TK_WE_COLS;
+    const bool e_ok = a.peer[H2D_E].buf != nullptr && a.peer[H2D_E].halo_c >= TK_WE_COLS;
+    we_batched = comm_edge && a.fw <= 8 && (g.cols & 3) == 0 && g.cols >= 2 * TK_WE_COLS && (w_ok || e_ok) &&
+                 (a.peer[H2D_W].buf == nullptr || w_ok) && (a.peer[H2D_E].buf == nullptr || e_ok);
     if (we_batched && smask == 15) {
-      if (a.peer[H2D_W].buf != nullptr && (j0 == 0 || j0 == 4)) we_half = j0 >> 2;
-      if (a.peer[H2D_E].buf != nullptr && (j0 == g.cols - 8 || j0 == g.cols - 4))
-        we_half = 2 + ((j0 - (g.cols - 8)) >> 2);
+      if (w_ok && j0 >= 0 && j0 < TK_WE_COLS) we_piece = j0 >> 2;
+      if (e_ok && j0 >= g.cols - TK_WE_COLS && j0 < g.cols) we_piece = 8 + ((j0 - (g.cols - TK_WE_COLS)) >> 2);
     }
     if (we_batched) {
 #pragma unroll
-      for (int h = 0; h < 4; ++h)
-        if (__ballot_sync(0xffffffffu, we_half == h) != 0u) we_own |= 1 << h;
+      for (int h = 0; h < 16; ++h)
+        if (__ballot_sync(0xffffffffu, we_piece == h) != 0u) we_own |= 1 << h;
       if (we_own == 0) we_batched = false;   // this strip holds no band column
     }
   }
@@ -330,8 +337,9 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
     }
     if (EXTRAS && we_batched && (unsigned)ro < (unsigned)n_out) {
       if (we_count == 0) we_rho0 = r_lo + ro;
-      if (we_half >= 0) {
-        const uint32_t slot = we_stage + (uint32_t)((((we_half >> 1) * TK_WE_ROWS + we_count) * 2 + (we_half & 1)) * 16);
+      if (we_piece >= 0) {
+        const uint32_t slot =
+            we_stage + (uint32_t)((((we_piece >> 3) * TK_WE_ROWS + we_count) * TK_WE_Q + (we_piece & 7)) * 16);
         asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(slot), "f"(fin.x), "f"(fin.y),
                      "f"(fin.z), "f"(fin.w) : "memory");
       }
