@@ -384,7 +384,10 @@ struct TkBounds {
   static constexpr int min_blocks = (K <= 5) ? 4 : 3;
 };
 
-template <int K, int ARITH, bool IMM>
+// XTR = false: a launch with neither peers nor a convergence norm (the common single-GPU
+// launch): the kernel contains no forwarding / reduction code at all, so that code cannot
+// cost the hot loop registers.
+template <int K, int ARITH, bool IMM, bool XTR>
 __global__ void __launch_bounds__(TK_WARPS * 32, TkBounds<K>::min_blocks)
 tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
@@ -410,7 +413,7 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
     __syncwarp();
     const int2 tk = a.tasks[task];
     const int strip = tk.x & 0x7fffffff;
-    const bool comm_edge = (tk.x < 0) && a.has_peers;
+    const bool comm_edge = XTR && (tk.x < 0) && a.has_peers;
     const int chunk = tk.y;
 
     if (comm_edge && (a.debug & 2)) {
@@ -441,11 +444,11 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
     const int jb = strip * a.wv - a.H;
     const bool frozen = (g.x0 + r_lo - K < g.ax_lo) || (g.x0 + r_hi - 1 + K > g.ax_hi) ||
                         (g.y0 + jb < g.ay_lo) || (g.y0 + jb + TK_W - 1 > g.ay_hi);
-    const bool extras = comm_edge || a.norm != H2D_NORM_NONE;
-    if (extras && frozen) {
-      acc = run_task<K, ARITH, IMM, true, true>(&tmap, a, strip, chunk, comm_edge, ring, bars, we_stage, lane);
-    } else if (extras) {
-      acc = run_task<K, ARITH, IMM, false, true>(&tmap, a, strip, chunk, comm_edge, ring, bars, we_stage, lane);
+    const bool extras = XTR && (comm_edge || a.norm != H2D_NORM_NONE);
+    if (XTR && extras && frozen) {
+      acc = run_task<K, ARITH, IMM, true, XTR>(&tmap, a, strip, chunk, comm_edge, ring, bars, we_stage, lane);
+    } else if (XTR && extras) {
+      acc = run_task<K, ARITH, IMM, false, XTR>(&tmap, a, strip, chunk, comm_edge, ring, bars, we_stage, lane);
     } else if (frozen) {
       acc = run_task<K, ARITH, IMM, true, false>(&tmap, a, strip, chunk, false, ring, bars, we_stage, lane);
     } else {
@@ -469,7 +472,7 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
     }
   }
 
-  if (a.norm == H2D_NORM_NONE) return;
+  if (!XTR || a.norm == H2D_NORM_NONE) return;
   // Deterministic two-level reduction: warp -> CTA -> last CTA.
   const bool l2 = a.norm == H2D_NORM_L2SQ;
   acc = l2 ? warp_sum(acc) : warp_max(acc);
@@ -504,28 +507,34 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
 
 typedef void (*tk_fn_t)(const CUtensorMap, const TkArgs);
 
-template <int ARITH, bool IMM>
+template <int ARITH, bool IMM, bool XTR>
 static tk_fn_t tk_pick_k(int k) {
   switch (k) {
-    case 1: return tk_kernel<1, ARITH, IMM>;
-    case 2: return tk_kernel<2, ARITH, IMM>;
-    case 3: return tk_kernel<3, ARITH, IMM>;
-    case 4: return tk_kernel<4, ARITH, IMM>;
-    case 5: return tk_kernel<5, ARITH, IMM>;
-    case 6: return tk_kernel<6, ARITH, IMM>;
-    case 7: return tk_kernel<7, ARITH, IMM>;
-    case 8: return tk_kernel<8, ARITH, IMM>;
+    case 1: return tk_kernel<1, ARITH, IMM, XTR>;
+    case 2: return tk_kernel<2, ARITH, IMM, XTR>;
+    case 3: return tk_kernel<3, ARITH, IMM, XTR>;
+    case 4: return tk_kernel<4, ARITH, IMM, XTR>;
+    case 5: return tk_kernel<5, ARITH, IMM, XTR>;
+    case 6: return tk_kernel<6, ARITH, IMM, XTR>;
+    case 7: return tk_kernel<7, ARITH, IMM, XTR>;
+    case 8: return tk_kernel<8, ARITH, IMM, XTR>;
+    default: return nullptr;
+  }
+}
+template <bool XTR>
+static tk_fn_t tk_pick_x(int k, int arith, bool imm) {
+  switch (arith) {
+    case H2D_ARITH_FP32:
+      return imm ? tk_pick_k<H2D_ARITH_FP32, true, XTR>(k) : tk_pick_k<H2D_ARITH_FP32, false, XTR>(k);
+    case H2D_ARITH_STRICT: return tk_pick_k<H2D_ARITH_STRICT, false, XTR>(k);
+    case H2D_ARITH_STRICT_FMA: return tk_pick_k<H2D_ARITH_STRICT_FMA, false, XTR>(k);
     default: return nullptr;
   }
 }
 // `imm`: fp32 mode with exactly the reference coefficients -> immediate-operand kernels.
-static tk_fn_t tk_pick(int k, int arith, bool imm) {
-  switch (arith) {
-    case H2D_ARITH_FP32: return imm ? tk_pick_k<H2D_ARITH_FP32, true>(k) : tk_pick_k<H2D_ARITH_FP32, false>(k);
-    case H2D_ARITH_STRICT: return tk_pick_k<H2D_ARITH_STRICT, false>(k);
-    case H2D_ARITH_STRICT_FMA: return tk_pick_k<H2D_ARITH_STRICT_FMA, false>(k);
-    default: return nullptr;
-  }
+// `xtr`: the launch forwards halos and/or reduces a norm.
+static tk_fn_t tk_pick(int k, int arith, bool imm, bool xtr) {
+  return xtr ? tk_pick_x<true>(k, arith, imm) : tk_pick_x<false>(k, arith, imm);
 }
 
 static bool coef_is_reference(const Geo& g, int arith) {
@@ -773,8 +782,10 @@ h2d_plan_t* h2d_plan_create(const h2d_plan_desc_t* d) {
   }
   // Opt in to the dynamic shared memory size once per kernel variant.
   for (int k = 1; k <= d->kmax; ++k) {
-    tk_fn_t fn = tk_pick(k, d->phys.arith, coef_is_reference(p->geo, d->phys.arith));
-    cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, TK_SMEM_BYTES);
+    for (int x = 0; x < 2; ++x) {
+      tk_fn_t fn = tk_pick(k, d->phys.arith, coef_is_reference(p->geo, d->phys.arith), x != 0);
+      cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, TK_SMEM_BYTES);
+    }
   }
   return p;
 }
@@ -791,7 +802,8 @@ int h2d_plan_launch_ex(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int
     return h2d_fail(H2D_EINVAL, "h2d_plan_launch: k = %d outside [1, kmax = %d]", k, p->desc.kmax);
   if (norm < H2D_NORM_NONE || norm > H2D_NORM_LINF)
     return h2d_fail(H2D_EINVAL, "h2d_plan_launch: unknown norm %d", norm);
-  tk_fn_t fn = tk_pick(k, p->desc.phys.arith, coef_is_reference(p->geo, p->desc.phys.arith));
+  const bool xtr = p->has_peers || norm != H2D_NORM_NONE;
+  tk_fn_t fn = tk_pick(k, p->desc.phys.arith, coef_is_reference(p->geo, p->desc.phys.arith), xtr);
   if (!fn) return h2d_fail(H2D_EINVAL, "h2d_plan_launch: no kernel for k = %d", k);
   const int H = round_up4(k);
   const TaskList& tl = p->lists[H / 4];
