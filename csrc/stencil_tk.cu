@@ -802,7 +802,11 @@ int h2d_plan_launch_ex(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int
     return h2d_fail(H2D_EINVAL, "h2d_plan_launch: k = %d outside [1, kmax = %d]", k, p->desc.kmax);
   if (norm < H2D_NORM_NONE || norm > H2D_NORM_LINF)
     return h2d_fail(H2D_EINVAL, "h2d_plan_launch: unknown norm %d", norm);
+#ifdef H2D_TK_FORCE_XTR
+  const bool xtr = true;
+#else
   const bool xtr = p->has_peers || norm != H2D_NORM_NONE;
+#endif
   tk_fn_t fn = tk_pick(k, p->desc.phys.arith, coef_is_reference(p->geo, p->desc.phys.arith), xtr);
   if (!fn) return h2d_fail(H2D_EINVAL, "h2d_plan_launch: no kernel for k = %d", k);
   const int H = round_up4(k);
