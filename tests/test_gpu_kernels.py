@@ -289,3 +289,20 @@ def test_config1_on_the_gpu_matches_the_reference_final_dat(tmp_path):
     except Exception as e:  # reference not staged / no gcc on this box
         pytest.skip(f"reference run unavailable: {e}")
     assert (tmp_path / "final.dat").read_bytes() == (tmp_path / "gpu_final.dat").read_bytes()
+
+
+def test_strict_mode_handles_zero_subnormal_and_huge_values():
+    # the strict kernels convert float -> double with integer instructions for normal
+    # numbers and with the hardware conversion otherwise: exercise both, bit-exactly
+    nx, ny = 64, 160
+    rng = np.random.default_rng(5)
+    u0 = rng.random((nx, ny), dtype=np.float32)
+    u0[:, :40] *= np.float32(1e-42)            # subnormals
+    u0[:, 40:80] = 0.0
+    u0[:, 80:120] *= np.float32(3e37)
+    u0[10:20, :] *= np.float32(-1.0)
+    for arith in ("strict", "strict-fma"):
+        s = Heat2DSolver(HeatConfig(nx=nx, ny=ny, steps=16, k=8, arith=arith, boundary="ghost-ring",
+                                    chunk_rows=16), DEV).load(u0)
+        s.run()
+        assert np.array_equal(s.gather().numpy(), oracle(nx, ny, 16, "ghost-ring", arith, u0=u0))
