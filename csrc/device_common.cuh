@@ -50,20 +50,6 @@ inline Geo make_geo(const h2d_tile_t& t, const h2d_phys_t& p) {
 }
 
 // ---------------------------------------------------------------- arithmetic
-// Exact float -> double without F2F.F64.F32 (a quarter-rate conversion-pipe
-// instruction; the strict kernels need three per point): normal numbers are
-// re-biased with five integer-pipe instructions, zero / subnormal / inf / nan take
-// the hardware conversion.  Bit-identical to (double)f for every input.
-__device__ __forceinline__ double f2d_exact(float f) {
-  const uint32_t b = __float_as_uint(f);
-  const uint32_t e = (b >> 23) & 0xffu;
-  if (e - 1u < 254u) {
-    const uint32_t hi = (b & 0x80000000u) | ((e + 896u) << 20) | ((b & 0x007fffffu) >> 3);
-    return __hiloint2double((int)hi, (int)(b << 29));
-  }
-  return (double)f;
-}
-
 // One point.  Must round exactly like point<ARITH>() in oracle.cpp.
 //   xm/xp: rows above/below, ym/yp: left/right (contiguous index).
 template <int ARITH>
@@ -74,9 +60,11 @@ __device__ __forceinline__ float point(float c, float xm, float xp, float ym, fl
   if (ARITH == H2D_ARITH_FP32) {
     return __fmaf_rn(g.cx, ew, __fmaf_rn(g.cy, ns, __fmul_rn(g.a0, c)));
   } else {
-    const double dc = f2d_exact(c);
-    const double t1 = __fma_rn(-2.0, dc, f2d_exact(ew));  // exact product: same bits as ew - 2.0*c
-    const double t2 = __fma_rn(-2.0, dc, f2d_exact(ns));
+    // (Replacing the three F2F.F64.F32 by integer re-biasing of normal numbers was
+    // measured 2.8x SLOWER at k = 8 — branches and register pressure — and dropped.)
+    const double dc = (double)c;
+    const double t1 = __fma_rn(-2.0, dc, (double)ew);  // exact product: same bits as ew - 2.0*c
+    const double t2 = __fma_rn(-2.0, dc, (double)ns);
     double r;
     if (ARITH == H2D_ARITH_STRICT_FMA) {
       r = __fma_rn(g.dcy, t2, __fma_rn(g.dcx, t1, dc));
