@@ -211,6 +211,7 @@ def main():
                        "k": k, "backend": a.impl, "conv": bool(a.conv),
                        "l2": f"inputs larger than L2 ({nx * ny * 4 / world / 2**20:.0f} MiB per GPU per buffer vs 126 MiB)"},
             "clocks": cs.summary(), "gpu_launches": launches, "impl": a.impl, "numa": numa,
+            "halo_wait_us_rank0": (solver.halo_wait_stats()[0] if hasattr(solver, "halo_wait_stats") else None),
             "baseline_ref": "10.1 GLUP/s = best published reference number (grad1612 MPI, 2560x2048, 160 ranks, "
                             "Report.pdf p21); published CUDA number is 0.669 GLUP/s",
             "roofline": {"hbm_gbs_measured": _peaks().get("hbm_gbs"),

@@ -76,6 +76,7 @@ struct TkArgs {
   // convergence check stopped the run (set by norm_finish_kernel).
   const uint32_t* ctl;
   uint32_t run_if;
+  unsigned long long* stats;   // [0] ns spent waiting for neighbour flags, [1] number of waits that blocked
   int32_t debug;   // bit 0: skip the peer stores (timing experiments only; H2D_DEBUG_NOFWD=1)
                    // bit 1: random per-task delays around the flag protocol (H2D_DEBUG_DELAY=1)
 };
@@ -429,7 +430,12 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
       if (lane == 0) {
         for (int d = 0; d < H2D_NDIR; ++d) {
           if (a.peer[d].buf == nullptr) continue;
+          // fast path: the neighbour published long ago (its edge tasks run first)
+          if ((int32_t)(ld_acquire_sys(a.flags_in + d) - (a.epoch - 1u)) >= 0) continue;
+          const uint64_t t0 = globaltimer_ns();
           if (!wait_flag_ge(a.flags_in + d, a.epoch - 1u, a.timeout_ns)) atomicExch(a.fault, 1u + d);
+          atomicAdd(a.stats, (unsigned long long)(globaltimer_ns() - t0));   // the mpiP "Waitall" row
+          atomicAdd(a.stats + 1, 1ull);
         }
         asm volatile("fence.proxy.async;" ::: "memory");
       }
@@ -840,6 +846,7 @@ int h2d_plan_launch_ex(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int
   a.done_counter = hdr + 1;
   a.norm_out = (float*)(hdr + 2);
   a.fault = hdr + 3;
+  a.stats = (unsigned long long*)(hdr + 8);
   a.cta_partials = (float*)((char*)p->scratch + 256);
   a.norm = norm;
   a.timeout_ns = p->desc.spin_timeout_ns > 0 ? p->desc.spin_timeout_ns : 10000000000LL;
@@ -879,5 +886,6 @@ int h2d_plan_run_many(h2d_plan_t* const* plans, int n_plans, int src_parity, int
 int64_t h2d_plan_launch_count(const h2d_plan_t* p) { return p ? p->launches : 0; }
 float* h2d_plan_norm_ptr(h2d_plan_t* p) { return p ? (float*)((unsigned*)p->scratch + 2) : nullptr; }
 uint32_t* h2d_plan_fault_ptr(h2d_plan_t* p) { return p ? (uint32_t*)p->scratch + 3 : nullptr; }
+uint64_t* h2d_plan_stats_ptr(h2d_plan_t* p) { return p ? (uint64_t*)((uint32_t*)p->scratch + 8) : nullptr; }
 
 }  // extern "C"

@@ -107,6 +107,10 @@ def main(argv=None) -> int:
             if dname not in ("prtdat", "rowmajor", "binary"):
                 raise ConfigError(f"unknown dump format {dname!r}")
         cfg = cfg.replace(dump="none")  # dumps are handled here, formats validated above
+        if a.preset == "mpi_heat2Dn" and not 3 <= cfg.px * cfg.py <= 8 and cfg.backend != "cpu":
+            # MINWORKER / MAXWORKER of the given program (mpi_heat2Dn.c:32-33,72-78); the master
+            # of the reference does no compute, so "workers" are this framework's ranks
+            raise ConfigError("ERROR: the number of tasks must be between 4 and 9.")
         if cfg.ref_conv_bug and cfg.conv:
             # the stale loop variable equals the tile height after the interior sweep
             fires = (cfg.nx // cfg.px) % cfg.interval == 0

@@ -149,6 +149,7 @@ class TileEngine:
         self.vals_ptrs = torch.tensor(all_vals_ptrs, dtype=torch.int64, device=f.device)
         self.flags_ptrs = torch.tensor(all_nflags_ptrs, dtype=torch.int64, device=f.device)
         self._fault = tensor_from_ptr(self.plan.fault_ptr, (1,), torch.int32, f.device)
+        self._stats = tensor_from_ptr(self.plan.stats_ptr, (2,), torch.int64, f.device)
 
     def launch(self, parity: int, k: int, epoch: int, norm: str, run_if: int = 0):
         self.plan.launch(parity, k, epoch, norm, self.ctl.data_ptr(), run_if)
@@ -167,6 +168,12 @@ class TileEngine:
 
     def fault(self) -> int:
         return int(self._fault.item())
+
+    def halo_wait_stats(self):
+        """(microseconds edge tasks spent blocked on neighbour flags, number of blocking waits)
+        accumulated since the plan was created."""
+        ns, n = (int(x) for x in self._stats.tolist())
+        return ns / 1e3, n
 
 
 class Heat2DSolver:
@@ -434,6 +441,11 @@ class Heat2DSolver:
 
     def owned_views(self) -> List[torch.Tensor]:
         return [f.owned(self.parity) for f in self.fields]
+
+    def halo_wait_stats(self):
+        """Sum over this process's tiles of (us blocked on neighbour flags, blocking waits)."""
+        tot = [e.halo_wait_stats() for e in self.engines]
+        return sum(t[0] for t in tot), sum(t[1] for t in tot)
 
     @property
     def kernel_launches(self) -> int:

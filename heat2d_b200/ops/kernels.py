@@ -229,6 +229,10 @@ class Plan:
     def fault_ptr(self) -> int:
         return int(self._lib.h2d_plan_fault_ptr(self._h))
 
+    @property
+    def stats_ptr(self) -> int:
+        return int(self._lib.h2d_plan_stats_ptr(self._h))
+
     def close(self):
         if getattr(self, "_h", None):
             self._lib.h2d_plan_destroy(self._h)

@@ -226,6 +226,10 @@ float* h2d_plan_norm_ptr(h2d_plan_t* plan);
 /* Device address of the watchdog word: non-zero after a flag wait timed out
  * (value = 1 + direction that stalled). */
 uint32_t* h2d_plan_fault_ptr(h2d_plan_t* plan);
+/* Device address of two 64-bit counters: [0] nanoseconds edge tasks spent blocked on a
+ * neighbour's epoch flag, [1] how many such waits blocked at all — the in-kernel
+ * counterpart of the MPI_Waitall row of the reference's mpiP profile (Report.pdf p35-37). */
+uint64_t* h2d_plan_stats_ptr(h2d_plan_t* plan);
 
 /* ---- resident solver: whole grid in the shared memory of one cluster ------ */
 /* All `steps` steps in ONE launch; halo rows travel between the CTAs of the

@@ -87,3 +87,11 @@ def test_restart_continues_a_run(tmp_path):
     want = K.cpu_initial_grid(24, 20, "exact")
     K.cpu_run(want, 50, N.make_phys(0.1, 0.1, "fixed", "fp32"))
     assert np.array_equal(D.read_binary(str(b / "final_binary.dat"), 24, 20), want)
+
+
+def test_given_program_worker_limits():
+    # MINWORKER 3 / MAXWORKER 8 (mpi_heat2Dn.c:32-33): enforced for the preset on device backends
+    a = build_parser().parse_args(["--preset", "mpi_heat2Dn", "--px", "2"])
+    assert config_from_args(a).px == 2
+    r = run_cli("--preset", "mpi_heat2Dn", "--px", "2", "--backend", "fused")
+    assert r.returncode == 1 and "between 4 and 9" in r.stderr

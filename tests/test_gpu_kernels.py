@@ -306,3 +306,11 @@ def test_strict_mode_handles_zero_subnormal_and_huge_values():
                                     chunk_rows=16), DEV).load(u0)
         s.run()
         assert np.array_equal(s.gather().numpy(), oracle(nx, ny, 16, "ghost-ring", arith, u0=u0))
+
+
+def test_halo_wait_statistics_are_exposed():
+    s = Heat2DSolver(HeatConfig(nx=256, ny=384, steps=32, k=8, px=2, py=2), DEV).initialize()
+    s.run()
+    us, n = s.halo_wait_stats()
+    # ranks emulated on one stream never block: every flag is already published
+    assert us == 0 and n == 0
