@@ -59,6 +59,8 @@ struct TkArgs {
   float* dst;
   const int2* tasks;     // .x = strip | (comm_edge << 31), .y = chunk
   int32_t n_tasks, n_chunks, chunk_rows, n_comm_edge;
+  int32_t row_base, row_end;   // rows [row_base, row_end) are processed; chunk c starts at row_base + c*R
+  int32_t n_strips;            // tasks == nullptr: task -> (task % n_strips, task / n_strips)
   int32_t H, wv, fw;     // column overlap, stored columns per strip, forwarded band width
   int32_t has_peers;
   PeerDev peer[H2D_NDIR];
@@ -201,8 +203,8 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
                                           uint32_t bars, uint32_t we_stage, int lane) {
   const Geo& g = a.g;
   const int R = a.chunk_rows;
-  const int r_lo = chunk * R;
-  const int r_hi = (chunk == a.n_chunks - 1) ? g.rows : r_lo + R;
+  const int r_lo = a.row_base + chunk * R;
+  const int r_hi = min(r_lo + R, a.row_end);
   const int n_out = r_hi - r_lo;
   const int jbase = strip * a.wv - a.H;  // tile-local column of lane 0, element 0
   const int j0 = jbase + lane * 4;
@@ -412,7 +414,7 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    const int2 tk = a.tasks[task];
+    const int2 tk = a.tasks != nullptr ? a.tasks[task] : make_int2(task % a.n_strips, task / a.n_strips);
     const int strip = tk.x & 0x7fffffff;
     const bool comm_edge = XTR && (tk.x < 0) && a.has_peers;
     const int chunk = tk.y;
@@ -445,8 +447,8 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
     // Does the footprint (all K levels) stay inside the updated region?
     const Geo& g = a.g;
     const int R = a.chunk_rows;
-    const int r_lo = chunk * R;
-    const int r_hi = (chunk == a.n_chunks - 1) ? g.rows : r_lo + R;
+    const int r_lo = a.row_base + chunk * R;
+    const int r_hi = min(r_lo + R, a.row_end);
     const int jb = strip * a.wv - a.H;
     const bool frozen = (g.x0 + r_lo - K < g.ax_lo) || (g.x0 + r_hi - 1 + K > g.ax_hi) ||
                         (g.y0 + jb < g.ay_lo) || (g.y0 + jb + TK_W - 1 > g.ay_hi);
@@ -569,6 +571,9 @@ struct h2d_plan {
   int64_t launches = 0;
   int device = 0;
   bool has_peers = false;
+  // lazily created by h2d_plan_solve_pipelined
+  cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+  std::vector<cudaEvent_t> ev_pool;
 };
 
 static inline int round_up4(int k) { return (k + 3) & ~3; }
@@ -701,6 +706,9 @@ void h2d_plan_destroy(h2d_plan_t* p) {
   for (auto& l : p->lists)
     if (l.dev) cudaFree(l.dev);
   if (p->own_scratch && p->scratch) cudaFree(p->scratch);
+  for (cudaEvent_t e : p->ev_pool) cudaEventDestroy(e);
+  if (p->s_h2d) cudaStreamDestroy(p->s_h2d);
+  if (p->s_d2h) cudaStreamDestroy(p->s_d2h);
   delete p;
 }
 
@@ -826,6 +834,9 @@ int h2d_plan_launch_ex(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int
   a.n_tasks = tl.n_tasks;
   a.n_chunks = p->n_chunks;
   a.chunk_rows = p->chunk_rows;
+  a.row_base = 0;
+  a.row_end = p->desc.tile.rows;
+  a.n_strips = tl.n_strips;
   a.n_comm_edge = tl.n_comm_edge;
   a.H = H;
   a.wv = TK_W - 2 * H;
@@ -880,6 +891,157 @@ int h2d_plan_run_many(h2d_plan_t* const* plans, int n_plans, int src_parity, int
         return rc;
     par ^= 1;
   }
+  return H2D_OK;
+}
+
+// One k-step launch restricted to owned rows [row_base, row_end) of a single tile
+// (no peers, no norm): tasks are enumerated arithmetically, chunk c starts at
+// row_base + c * R.
+static int launch_window(h2d_plan* p, int src_parity, int k, int row_base, int row_end, cudaStream_t st) {
+  if (row_end <= row_base) return H2D_OK;
+  tk_fn_t fn = tk_pick(k, p->desc.phys.arith, coef_is_reference(p->geo, p->desc.phys.arith), false);
+  if (!fn) return h2d_fail(H2D_EINVAL, "launch_window: no kernel for k = %d", k);
+  const int H = round_up4(k);
+  TkArgs a;
+  memset(&a, 0, sizeof a);
+  a.g = p->geo;
+  a.dst = p->desc.buf[1 - src_parity];
+  a.tasks = nullptr;
+  a.chunk_rows = p->chunk_rows;
+  a.row_base = row_base;
+  a.row_end = row_end;
+  a.H = H;
+  a.wv = TK_W - 2 * H;
+  a.n_strips = (p->desc.tile.cols + a.wv - 1) / a.wv;
+  a.n_chunks = (row_end - row_base + a.chunk_rows - 1) / a.chunk_rows;
+  a.n_tasks = a.n_strips * a.n_chunks;
+  a.fw = p->fw;
+  unsigned* hdr = (unsigned*)p->scratch;
+  a.edge_counter = hdr + 0;
+  a.done_counter = hdr + 1;
+  a.norm_out = (float*)(hdr + 2);
+  a.fault = hdr + 3;
+  a.stats = (unsigned long long*)(hdr + 8);
+  a.cta_partials = (float*)((char*)p->scratch + 256);
+  a.timeout_ns = 10000000000LL;
+  const int grid = (a.n_tasks + TK_WARPS - 1) / TK_WARPS;
+  fn<<<grid, TK_WARPS * 32, TK_SMEM_BYTES, st>>>(p->tmap[src_parity], a);
+  H2D_CHECK_LAUNCH("tk_kernel (row window)");
+  p->launches++;
+  return H2D_OK;
+}
+
+int h2d_plan_solve_pipelined(h2d_plan_t* p, const float* host_in, int64_t in_pitch, float* host_out,
+                             int64_t out_pitch, int64_t steps, int k, int block_rows, int skew_rows,
+                             void* stream, int* final_parity) {
+  if (!p || !host_in || !host_out || steps < 0)
+    return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: bad argument");
+  if (p->has_peers) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: single-tile plans only");
+  if (k < 1 || k > p->desc.kmax) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: k = %d outside [1, %d]", k, p->desc.kmax);
+  const h2d_tile_t& t = p->desc.tile;
+  if (in_pitch < t.cols || out_pitch < t.cols) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: host pitch < cols");
+  const int rows = t.rows;
+  const int R = p->chunk_rows;
+  const int S = skew_rows > 0 ? skew_rows : 32;          // rows the processed window moves up per launch
+  if (S < k + 1) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: skew %d must exceed k = %d", S, k);
+  const int L = (int)((steps + k - 1) / k);              // launches ("levels") per block
+  int M = block_rows;
+  if (M <= 0) {                                          // about two waves of tasks per launch
+    const int wv = TK_W - 2 * round_up4(p->desc.kmax);
+    const int ns = (t.cols + wv - 1) / wv;
+    int m = (int)((2.0 * sm_count() * (p->desc.kmax <= 5 ? 16 : 12)) / ns);
+    if (m < 1) m = 1;
+    M = m * R;
+  }
+  if (M > rows) M = rows;
+  cudaStream_t cs = (cudaStream_t)stream;
+  if (!p->s_h2d) H2D_CUDA_TRY(cudaStreamCreateWithFlags(&p->s_h2d, cudaStreamNonBlocking));
+  if (!p->s_d2h) H2D_CUDA_TRY(cudaStreamCreateWithFlags(&p->s_d2h, cudaStreamNonBlocking));
+  size_t ev_used = 0;
+  auto new_event = [&](cudaEvent_t* out) -> int {
+    if (ev_used == p->ev_pool.size()) {
+      cudaEvent_t e;
+      H2D_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+      p->ev_pool.push_back(e);
+    }
+    *out = p->ev_pool[ev_used++];
+    return H2D_OK;
+  };
+  auto dev_row = [&](int parity, int r) -> float* {
+    return p->desc.buf[parity] + (int64_t)(r + t.halo_r) * t.pitch + t.halo_c;
+  };
+
+  // the copy streams start after whatever the caller queued on `stream`
+  cudaEvent_t e_start;
+  if (int rc = new_event(&e_start)) return rc;
+  H2D_CUDA_TRY(cudaEventRecord(e_start, cs));
+  H2D_CUDA_TRY(cudaStreamWaitEvent(p->s_h2d, e_start, 0));
+  H2D_CUDA_TRY(cudaStreamWaitEvent(p->s_d2h, e_start, 0));
+
+  // upload in units of U rows, one event per unit
+  const int U = M < 1024 ? M : 1024;
+  const int n_units = (rows + U - 1) / U;
+  std::vector<cudaEvent_t> up(n_units);
+  for (int u = 0; u < n_units; ++u) {
+    const int r0 = u * U, r1 = r0 + U < rows ? r0 + U : rows;
+    H2D_CUDA_TRY(cudaMemcpy2DAsync(dev_row(0, r0), (size_t)t.pitch * 4, host_in + (int64_t)r0 * in_pitch,
+                                   (size_t)in_pitch * 4, (size_t)t.cols * 4, (size_t)(r1 - r0),
+                                   cudaMemcpyHostToDevice, p->s_h2d));
+    if (int rc = new_event(&up[u])) return rc;
+    H2D_CUDA_TRY(cudaEventRecord(up[u], p->s_h2d));
+  }
+
+  const int out_par = L & 1;
+  int waited = -1;                                       // last upload unit the compute stream waits for
+  const int64_t span = (int64_t)rows + (int64_t)S * (L > 0 ? L - 1 : 0);
+  const int n_blocks = L > 0 ? (int)((span + M - 1) / M) : 0;
+  int d2h_done_rows = 0;                                 // rows [0, d2h_done_rows) already queued for download
+  for (int b = 0; b < n_blocks; ++b) {
+    // level 0 of this block reads rows below (b+1)*M + k
+    int need_row = (b + 1) * M + k;
+    if (need_row > rows) need_row = rows;
+    const int need_unit = (need_row - 1) / U;
+    if (need_unit > waited) {
+      H2D_CUDA_TRY(cudaStreamWaitEvent(cs, up[need_unit], 0));
+      waited = need_unit;
+    }
+    for (int e = 0; e < L; ++e) {
+      int64_t lo = (int64_t)b * M - (int64_t)S * e, hi = lo + M;
+      if (hi <= 0 || lo >= rows) continue;
+      if (lo < 0) lo = 0;
+      if (hi > rows) hi = rows;
+      const int kk = (e < L - 1) ? k : (int)(steps - (int64_t)(L - 1) * k);
+      if (int rc = launch_window(p, e & 1, kk, (int)lo, (int)hi, cs)) return rc;
+    }
+    // rows below (b+1)*M - S*(L-1) now hold the final field
+    int64_t fin = (int64_t)(b + 1) * M - (int64_t)S * (L - 1);
+    if (b == n_blocks - 1 || fin > rows) fin = rows;
+    if (fin > d2h_done_rows) {
+      cudaEvent_t ev;
+      if (int rc = new_event(&ev)) return rc;
+      H2D_CUDA_TRY(cudaEventRecord(ev, cs));
+      H2D_CUDA_TRY(cudaStreamWaitEvent(p->s_d2h, ev, 0));
+      H2D_CUDA_TRY(cudaMemcpy2DAsync(host_out + (int64_t)d2h_done_rows * out_pitch, (size_t)out_pitch * 4,
+                                     dev_row(out_par, d2h_done_rows), (size_t)t.pitch * 4, (size_t)t.cols * 4,
+                                     (size_t)(fin - d2h_done_rows), cudaMemcpyDeviceToHost, p->s_d2h));
+      d2h_done_rows = (int)fin;
+    }
+  }
+  if (L == 0) {  // nothing to compute: upload, then download the same field
+    H2D_CUDA_TRY(cudaStreamWaitEvent(p->s_d2h, up[n_units - 1], 0));
+    H2D_CUDA_TRY(cudaMemcpy2DAsync(host_out, (size_t)out_pitch * 4, dev_row(0, 0), (size_t)t.pitch * 4,
+                                   (size_t)t.cols * 4, (size_t)rows, cudaMemcpyDeviceToHost, p->s_d2h));
+  }
+  // the caller's stream completes when the last download has
+  cudaEvent_t e_end;
+  if (int rc = new_event(&e_end)) return rc;
+  H2D_CUDA_TRY(cudaEventRecord(e_end, p->s_d2h));
+  H2D_CUDA_TRY(cudaStreamWaitEvent(cs, e_end, 0));
+  cudaEvent_t e_end2;
+  if (int rc = new_event(&e_end2)) return rc;
+  H2D_CUDA_TRY(cudaEventRecord(e_end2, p->s_h2d));
+  H2D_CUDA_TRY(cudaStreamWaitEvent(cs, e_end2, 0));
+  if (final_parity) *final_parity = out_par;
   return H2D_OK;
 }
 

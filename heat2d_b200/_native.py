@@ -130,6 +130,8 @@ def cuda():
             lib.h2d_plan_launch_ex.argtypes = [vp, C.c_int, C.c_int, C.c_uint32, C.c_int, vp, C.c_uint32, vp]
             lib.h2d_plan_run_many.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32,
                                               C.POINTER(vp), vp]
+            lib.h2d_plan_solve_pipelined.argtypes = [vp, vp, C.c_int64, vp, C.c_int64, C.c_int64, C.c_int, C.c_int,
+                                                     C.c_int, vp, C.POINTER(C.c_int)]
             lib.h2d_plan_launch_count.argtypes = [vp]
             lib.h2d_plan_launch_count.restype = C.c_int64
             lib.h2d_plan_norm_ptr.argtypes = [vp]

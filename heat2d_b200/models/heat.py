@@ -372,6 +372,30 @@ class Heat2DSolver:
         return RunResult(self.steps_done, iterations, converged, last_norm, elapsed, launches, checks,
                          cfg.nx, cfg.ny)
 
+    def solve_pipelined(self, host_in: torch.Tensor, host_out: torch.Tensor, steps: Optional[int] = None,
+                        block_rows: int = 0, skew_rows: int = 0) -> RunResult:
+        """End-to-end solve of a field that lives in (pinned) host memory: upload,
+        `steps` steps, download, with the three phases overlapped block by block
+        (one tile, no convergence test).  `elapsed_s` covers all three."""
+        cfg = self.cfg
+        steps = cfg.steps if steps is None else steps
+        if len(self.engines) != 1 or self.world != 1 or cfg.backend not in ("fused", "single"):
+            raise ValueError("solve_pipelined needs the fused backend on a single tile")
+        if cfg.conv:
+            raise ValueError("solve_pipelined has no convergence test; use run()")
+        plan = self.engines[0].plan
+        l0 = plan.launch_count
+        ev0 = torch.cuda.Event(enable_timing=True)
+        ev1 = torch.cuda.Event(enable_timing=True)
+        with torch.cuda.device(self.device):
+            ev0.record()
+            self.parity = plan.solve_pipelined(host_in, host_out, steps, cfg.k, block_rows, skew_rows)
+            ev1.record()
+            ev1.synchronize()
+        self.steps_done = cfg.start_step + steps
+        return RunResult(self.steps_done, self.steps_done, False, float("nan"), ev0.elapsed_time(ev1) / 1e3,
+                         plan.launch_count - l0, 0, cfg.nx, cfg.ny)
+
     def _run_plain(self, steps: int) -> RunResult:
         """Plain one-step kernel + standalone norm kernel, host-side decision (the
         structure of the reference loop; baseline for the fused path)."""

@@ -217,6 +217,25 @@ class Plan:
             N.check(lib, lib.h2d_plan_run_many(arr, len(plans), src_parity, k, n_launches,
                                                epoch0 & 0xFFFFFFFF, ctl, _stream_ptr(plans[0].device)))
 
+    def solve_pipelined(self, host_in: torch.Tensor, host_out: torch.Tensor, steps: int, k: int,
+                        block_rows: int = 0, skew_rows: int = 0) -> int:
+        """Upload `host_in`, advance `steps` steps, download into `host_out`, overlapped
+        (h2d_plan_solve_pipelined).  Both tensors: pinned, float32, (rows, cols), unit
+        column stride.  Returns the parity of the buffer that holds the result."""
+        for t_, nm in ((host_in, "host_in"), (host_out, "host_out")):
+            if t_.is_cuda or t_.dtype != torch.float32 or t_.dim() != 2 or t_.stride(1) != 1:
+                raise ValueError(f"{nm} must be a 2-D float32 host tensor with unit column stride")
+            if not t_.is_pinned():
+                raise ValueError(f"{nm} must be pinned (torch.Tensor.pin_memory) for the copies to overlap")
+            if tuple(t_.shape) != (self.tile.rows, self.tile.cols):
+                raise ValueError(f"{nm}: expected shape {(self.tile.rows, self.tile.cols)}, got {tuple(t_.shape)}")
+        par = C.c_int(0)
+        with torch.cuda.device(self.device):
+            N.check(self._lib, self._lib.h2d_plan_solve_pipelined(
+                self._h, host_in.data_ptr(), host_in.stride(0), host_out.data_ptr(), host_out.stride(0),
+                int(steps), int(k), int(block_rows), int(skew_rows), _stream_ptr(self.device), C.byref(par)))
+        return par.value
+
     @property
     def launch_count(self) -> int:
         return int(self._lib.h2d_plan_launch_count(self._h))

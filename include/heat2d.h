@@ -218,6 +218,23 @@ int h2d_plan_launch_ex(h2d_plan_t* plan, int src_parity, int k, uint32_t epoch, 
 int h2d_plan_run_many(h2d_plan_t* const* plans, int n_plans, int src_parity, int k, int n_launches,
                       uint32_t epoch0, const uint32_t* const* ctls /* per plan, or NULL */, void* stream);
 
+/* Upload, solve, download — overlapped.  For a single-tile plan: copies the nx x ny
+ * field `host_in` (pinned host memory, `in_pitch` floats per row) into buf[0], advances
+ * it `steps` steps in launches of k, and copies the result to `host_out`, with the
+ * three phases pipelined: the grid is cut into blocks of `block_rows` rows
+ * (0 = about two waves of tasks) and block b runs ALL its launches before block b+1
+ * starts, the window of launch e being shifted up by e * skew_rows rows
+ * (0 = 32; must exceed k) so that every launch finds its k halo rows already
+ * computed by the previous launch.  Block b can start as soon as its rows (and k
+ * more) have arrived, and its final rows leave while later blocks still compute.
+ * Everything is ordered on `stream` for the caller: when work queued on `stream`
+ * after this call runs, host_out is complete.  *final_parity = which buffer holds
+ * the result.  The reference has no counterpart: its CUDA program never moves the
+ * field across PCIe at all (grad1612_cuda_heat.cu:75-92).                        */
+int h2d_plan_solve_pipelined(h2d_plan_t* plan, const float* host_in, int64_t in_pitch, float* host_out,
+                             int64_t out_pitch, int64_t steps, int k, int block_rows, int skew_rows,
+                             void* stream, int* final_parity);
+
 /* Number of kernels launched by this plan since creation (bench bookkeeping). */
 int64_t h2d_plan_launch_count(const h2d_plan_t* plan);
 /* Device address of this rank's partial norm (1 float, valid after a launch
