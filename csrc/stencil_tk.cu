@@ -945,15 +945,17 @@ int h2d_plan_solve_pipelined(h2d_plan_t* p, const float* host_in, int64_t in_pit
   const int S = skew_rows > 0 ? skew_rows : 32;          // rows the processed window moves up per launch
   if (S < k + 1) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: skew %d must exceed k = %d", S, k);
   const int L = (int)((steps + k - 1) / k);              // launches ("levels") per block
-  int M = block_rows;
-  if (M <= 0) {                                          // about two waves of tasks per launch
-    const int wv = TK_W - 2 * round_up4(p->desc.kmax);
-    const int ns = (t.cols + wv - 1) / wv;
-    int m = (int)((2.0 * sm_count() * (p->desc.kmax <= 5 ? 16 : 12)) / ns);
-    if (m < 1) m = 1;
-    M = m * R;
-  }
-  if (M > rows) M = rows;
+  // Block sizes.  Large blocks compute efficiently (several waves of tasks per launch) but
+  // the first block delays the start by its upload and the last one exposes its download, so
+  // the sizes ramp up from one wave of tasks to `block_rows` (0 = four waves) and down again.
+  const int wv_ = TK_W - 2 * round_up4(p->desc.kmax);
+  const int ns_ = (t.cols + wv_ - 1) / wv_;
+  const double slots_ = (double)sm_count() * (p->desc.kmax <= 5 ? 16 : 12);
+  int m1 = (int)(slots_ / ns_);                           // chunks per launch for one wave
+  if (m1 < 1) m1 = 1;
+  const int M1 = m1 * R;
+  int M = block_rows > 0 ? block_rows : 4 * M1;
+  if (M < S + 1) M = S + 1;
   cudaStream_t cs = (cudaStream_t)stream;
   if (!p->s_h2d) H2D_CUDA_TRY(cudaStreamCreateWithFlags(&p->s_h2d, cudaStreamNonBlocking));
   if (!p->s_d2h) H2D_CUDA_TRY(cudaStreamCreateWithFlags(&p->s_d2h, cudaStreamNonBlocking));
@@ -979,7 +981,7 @@ int h2d_plan_solve_pipelined(h2d_plan_t* p, const float* host_in, int64_t in_pit
   H2D_CUDA_TRY(cudaStreamWaitEvent(p->s_d2h, e_start, 0));
 
   // upload in units of U rows, one event per unit
-  const int U = M < 1024 ? M : 1024;
+  const int U = M1 < 1024 ? (M1 < rows ? M1 : rows) : 1024;
   const int n_units = (rows + U - 1) / U;
   std::vector<cudaEvent_t> up(n_units);
   for (int u = 0; u < n_units; ++u) {
@@ -994,27 +996,50 @@ int h2d_plan_solve_pipelined(h2d_plan_t* p, const float* host_in, int64_t in_pit
   const int out_par = L & 1;
   int waited = -1;                                       // last upload unit the compute stream waits for
   const int64_t span = (int64_t)rows + (int64_t)S * (L > 0 ? L - 1 : 0);
-  const int n_blocks = L > 0 ? (int)((span + M - 1) / M) : 0;
+  // block boundaries over [0, span): ramp up, plateau of M, ramp down
+  std::vector<int64_t> bounds;
+  if (L > 0) {
+    std::vector<int64_t> ramp;
+    for (int64_t sz = M1; sz < M; sz *= 2) ramp.push_back(sz);
+    int64_t ramp_sum = 0;
+    for (int64_t v : ramp) ramp_sum += v;
+    bounds.push_back(0);
+    if (block_rows > 0 && block_rows <= M1) ramp.clear(), ramp_sum = 0;   // caller asked for small uniform blocks
+    if (2 * ramp_sum + M <= span) {
+      int64_t pos = 0;
+      for (int64_t v : ramp) { pos += v; bounds.push_back(pos); }
+      const int64_t mid_end = span - ramp_sum;
+      while (pos + M < mid_end) { pos += M; bounds.push_back(pos); }
+      if (mid_end > pos) { pos = mid_end; bounds.push_back(pos); }
+      for (size_t i = ramp.size(); i-- > 0;) { pos += ramp[i]; bounds.push_back(pos); }
+    } else {
+      int64_t pos = 0;
+      while (pos < span) { pos += M; bounds.push_back(pos < span ? pos : span); }
+    }
+    if (bounds.back() < span) bounds.push_back(span);
+  }
+  const int n_blocks = bounds.empty() ? 0 : (int)bounds.size() - 1;
   int d2h_done_rows = 0;                                 // rows [0, d2h_done_rows) already queued for download
   for (int b = 0; b < n_blocks; ++b) {
-    // level 0 of this block reads rows below (b+1)*M + k
-    int need_row = (b + 1) * M + k;
+    const int64_t b_lo = bounds[b], b_hi = bounds[b + 1];
+    // level 0 of this block reads rows below b_hi + k
+    int64_t need_row = b_hi + k;
     if (need_row > rows) need_row = rows;
-    const int need_unit = (need_row - 1) / U;
+    const int need_unit = (int)((need_row - 1) / U);
     if (need_unit > waited) {
       H2D_CUDA_TRY(cudaStreamWaitEvent(cs, up[need_unit], 0));
       waited = need_unit;
     }
     for (int e = 0; e < L; ++e) {
-      int64_t lo = (int64_t)b * M - (int64_t)S * e, hi = lo + M;
+      int64_t lo = b_lo - (int64_t)S * e, hi = b_hi - (int64_t)S * e;
       if (hi <= 0 || lo >= rows) continue;
       if (lo < 0) lo = 0;
       if (hi > rows) hi = rows;
       const int kk = (e < L - 1) ? k : (int)(steps - (int64_t)(L - 1) * k);
       if (int rc = launch_window(p, e & 1, kk, (int)lo, (int)hi, cs)) return rc;
     }
-    // rows below (b+1)*M - S*(L-1) now hold the final field
-    int64_t fin = (int64_t)(b + 1) * M - (int64_t)S * (L - 1);
+    // rows below b_hi - S*(L-1) now hold the final field
+    int64_t fin = b_hi - (int64_t)S * (L - 1);
     if (b == n_blocks - 1 || fin > rows) fin = rows;
     if (fin > d2h_done_rows) {
       cudaEvent_t ev;
