@@ -942,7 +942,7 @@ int h2d_plan_solve_pipelined(h2d_plan_t* p, const float* host_in, int64_t in_pit
   if (in_pitch < t.cols || out_pitch < t.cols) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: host pitch < cols");
   const int rows = t.rows;
   const int R = p->chunk_rows;
-  const int S = skew_rows > 0 ? skew_rows : 32;          // rows the processed window moves up per launch
+  const int S = skew_rows > 0 ? skew_rows : k + 4;       // rows the processed window moves up per launch
   if (S < k + 1) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: skew %d must exceed k = %d", S, k);
   const int L = (int)((steps + k - 1) / k);              // launches ("levels") per block
   // Block sizes.  Large blocks compute efficiently (several waves of tasks per launch) but

@@ -224,7 +224,7 @@ int h2d_plan_run_many(h2d_plan_t* const* plans, int n_plans, int src_parity, int
  * three phases pipelined: the grid is cut into blocks of `block_rows` rows
  * (0 = about two waves of tasks) and block b runs ALL its launches before block b+1
  * starts, the window of launch e being shifted up by e * skew_rows rows
- * (0 = 32; must exceed k) so that every launch finds its k halo rows already
+ * (0 = k + 4; must exceed k) so that every launch finds its k halo rows already
  * computed by the previous launch.  Block b can start as soon as its rows (and k
  * more) have arrived, and its final rows leave while later blocks still compute.
  * Everything is ordered on `stream` for the caller: when work queued on `stream`
