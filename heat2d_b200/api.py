@@ -36,8 +36,22 @@ def make_solver(cfg: HeatConfig, device=None):
 
 def solve(cfg: HeatConfig, u0=None, device=None, gather: bool = True) -> Tuple[object, Optional[torch.Tensor]]:
     """Initialise (or load `u0`, a full nx x ny host array), run `cfg.steps`
-    steps and return ``(RunResult, final field on the host or None)``."""
+    steps and return ``(RunResult, final field on the host or None)``.
+
+    A pinned float32 host tensor `u0` on one GPU (fused backend, no convergence
+    test) takes the pipelined path: upload, steps and download overlap block by
+    block (``Heat2DSolver.solve_pipelined``) and the returned field is pinned."""
     s = make_solver(cfg, device)
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    if (isinstance(u0, torch.Tensor) and not u0.is_cuda and u0.is_pinned() and u0.dtype == torch.float32
+            and world == 1 and cfg.backend in ("fused", "single") and not cfg.conv and cfg.px * cfg.py == 1
+            and hasattr(s, "solve_pipelined")):
+        try:
+            out = torch.empty((cfg.nx, cfg.ny), dtype=torch.float32).pin_memory()
+            res = s.solve_pipelined(u0, out, cfg.steps)
+            return res, out
+        finally:
+            s.close()
     try:
         if u0 is None:
             s.initialize()

@@ -334,3 +334,14 @@ def test_pipelined_upload_solve_download(shape, steps, k, block, skew):
     # and the solver can keep going from there with ordinary launches
     s.run(16)
     assert np.array_equal(s.gather().numpy(), oracle(nx, ny, steps + 16, u0=u0))
+
+
+def test_solve_api_uses_the_pipelined_path_for_pinned_input():
+    from heat2d_b200 import solve
+    nx, ny = 400, 640
+    u0 = rand_grid(nx, ny, 3)
+    res, field = solve(HeatConfig(nx=nx, ny=ny, steps=30, k=8), u0=torch.from_numpy(u0).pin_memory())
+    assert field.is_pinned() and res.steps_done == 30
+    assert np.array_equal(field.numpy(), oracle(nx, ny, 30, u0=u0))
+    res2, field2 = solve(HeatConfig(nx=nx, ny=ny, steps=30, k=8), u0=u0)      # ordinary path, numpy in
+    assert np.array_equal(field2.numpy(), field.numpy())
