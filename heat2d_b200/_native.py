@@ -82,7 +82,7 @@ def _declare_common(lib):
 
 
 def _load(path: Path):
-    return C.CDLL(str(path), mode=C.RTLD_GLOBAL if False else C.DEFAULT_MODE)
+    return C.CDLL(str(path))
 
 
 def cpu():

@@ -143,6 +143,8 @@ def main(argv=None) -> int:
         return 1
 
     from .utils import dump as D
+    from .utils.timing import PhaseTimer
+    timer = PhaseTimer(torch.cuda.current_device() if (cfg.backend != "cpu" and torch.cuda.is_available()) else None)
     style = a.preset or "grad1612_mpi"
     if rank == 0:
         _banner(cfg, world if world > 1 else cfg.px * cfg.py, style)
@@ -157,11 +159,12 @@ def main(argv=None) -> int:
             from .ops import kernels as K
             print(K.device_info(torch.cuda.current_device()))
 
-    if cfg.restart:
-        grid = D.read_binary(cfg.restart, cfg.nx, cfg.ny)
-        solver.load(grid)
-    else:
-        solver.initialize()
+    with timer.phase("init"):
+        if cfg.restart:
+            grid = D.read_binary(cfg.restart, cfg.nx, cfg.ny)
+            solver.load(grid)
+        else:
+            solver.initialize()
 
     def write(stem):
         if not dumps:
@@ -183,8 +186,10 @@ def main(argv=None) -> int:
     if rank == 0 and dumps:
         print("Writing initial.dat ..." if style != "mpi_heat2Dn"
               else "Initializing grid and writing initial.dat file...")
-    write("initial")
-    res = solver.run()
+    with timer.phase("dump_initial"):
+        write("initial")
+    with timer.phase("run"):
+        res = solver.run()
     if rank == 0:
         if style == "mpi_heat2Dn":
             print(f"Elapsed time: {res.elapsed_s:e} sec")
@@ -196,9 +201,10 @@ def main(argv=None) -> int:
             print(f"Exiting after {res.iterations} iterations\nElapsed time: {res.elapsed_s:e} sec")
             if dumps:
                 print("Writing final.dat ...")
-    write("final")
+    with timer.phase("dump_final"):
+        write("final")
     if rank == 0:
-        rec = {"config": cfg.to_dict(), "world": world, "steps_done": res.steps_done,
+        rec = {"phases": timer.as_dict(),"config": cfg.to_dict(), "world": world, "steps_done": res.steps_done,
                "iterations": res.iterations, "converged": res.converged, "last_norm": res.last_norm,
                "seconds_max_over_ranks": res.elapsed_s, "glups": res.glups, "launches": res.launches,
                "checks": res.checks, "when": time.strftime("%Y-%m-%dT%H:%M:%S")}

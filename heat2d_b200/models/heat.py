@@ -12,7 +12,6 @@ issued rank after rank on one stream.  The one-process-per-GPU version is
 """
 from __future__ import annotations
 
-import math
 from dataclasses import dataclass
 from typing import Dict, List, Optional
 
@@ -133,7 +132,6 @@ class TileEngine:
         self.spin_timeout_s = spin_timeout_s
         dev = field.device
         self.norm_total = torch.zeros(1, dtype=torch.float32, device=dev)
-        self.stop = torch.zeros(1, dtype=torch.int32, device=dev)
         # run-control word: 0 = iterating, q = check number q stopped the run
         self.ctl = torch.zeros(1, dtype=torch.int32, device=dev)
         self.plan: Optional[K.Plan] = None
