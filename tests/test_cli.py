@@ -17,9 +17,26 @@ from heat2d_b200.utils import dump as D
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+class _Res:
+    def __init__(self, rc, out, err):
+        self.returncode, self.stdout, self.stderr = rc, out, err
+
+
 def run_cli(*args):
-    return subprocess.run([sys.executable, "-m", "heat2d_b200", *args], cwd=ROOT, capture_output=True,
-                          text=True, timeout=300)
+    """Run the CLI in-process (the module entry point itself is covered by test_module_entry_point)."""
+    import contextlib
+    import io
+    from heat2d_b200.cli import main
+    out, err = io.StringIO(), io.StringIO()
+    with contextlib.redirect_stdout(out), contextlib.redirect_stderr(err):
+        rc = main(list(args))
+    return _Res(rc, out.getvalue(), err.getvalue())
+
+
+def test_module_entry_point(tmp_path):
+    r = subprocess.run([sys.executable, "-m", "heat2d_b200", "--backend", "cpu", "--out-dir", str(tmp_path)],
+                       cwd=ROOT, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "Problem size:10x10" in r.stdout
 
 
 def test_presets_cover_the_four_programs():

@@ -102,15 +102,29 @@ def test_grad1612_mpi_rejects_wrong_process_count(tmp_path):
         rb.run_mpi(exe, 2, tmp_path)
 
 
-def test_grad1612_hybrid_convergence_with_the_shipped_predicate(tmp_path):
+def test_grad1612_convergence_with_the_shipped_predicate(tmp_path):
     # 20x20 on one rank: the stale loop variable equals the tile height 20, 20 % INTERVAL == 0,
     # so the shipped code checks on EVERY step.  --ref-conv-bug replays that.
-    exe = rb.build_mpi("grad1612_hybrid", {"NXPROB": 20, "NYPROB": 20, "STEPS": 100000, "NUMTHREADS": 1}, "-O2")
+    exe = rb.build_mpi("grad1612_mpi", {"NXPROB": 20, "NYPROB": 20, "STEPS": 100000, "GRIDX": 1, "GRIDY": 1,
+                                        "CONVERGENCE": 1}, "-O2")
     out, _ = rb.run_mpi(exe, 1, tmp_path)
     it = int(re.search(r"Exiting after (\d+) iterations", out).group(1))
-    cfg = preset("grad1612_hybrid", backend="cpu", nx=20, ny=20, steps=100000, interval=1, threads=1)
+    cfg = preset("grad1612_mpi", backend="cpu", nx=20, ny=20, steps=100000, px=1, py=1, conv=True, interval=1)
     s = CpuSolver(cfg).initialize()
     res = s.run()
     assert res.converged and abs(res.steps_done - it) <= 1   # float vs double accumulation of the norm
     if res.steps_done == it:
         assert np.array_equal(D.read_binary(str(tmp_path / "final_binary.dat"), 20, 20), s.u)
+
+
+def test_grad1612_hybrid_runs_on_the_shim_and_matches(tmp_path):
+    # MPI + OpenMP program, one rank, one thread (the shipped nested pragmas make >1 thread
+    # redo the whole sweep per thread: same values, 4x the time — Report.pdf p24)
+    exe = rb.build_mpi("grad1612_hybrid", {"NXPROB": 24, "NYPROB": 20, "STEPS": 60, "NUMTHREADS": 1,
+                                           "CONVERGENCE": 0}, "-O2")
+    out, secs = rb.run_mpi(exe, 1, tmp_path)
+    assert secs is not None
+    cfg = preset("grad1612_hybrid", backend="cpu", nx=24, ny=20, steps=60, conv=False, threads=1)
+    s = CpuSolver(cfg).initialize()
+    s.run()
+    assert np.array_equal(D.read_binary(str(tmp_path / "final_binary.dat"), 24, 20), s.u)
