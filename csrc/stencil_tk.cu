@@ -232,6 +232,7 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
   // float4 is that piece of the W band, 8..15 = of the E band, -1 = not in a band.
   int we_piece = -1, we_own = 0, we_count = 0, we_rho0 = 0;
   bool we_batched = false;
+  bool we_perrow = false;   // W/E peers exist but their columns must go row by row
   if (EXTRAS) {
     const bool w_ok = a.peer[H2D_W].buf != nullptr && a.peer[H2D_W].halo_c >= TK_WE_COLS;
     const bool e_ok = a.peer[H2D_E].buf != nullptr && a.peer[H2D_E].halo_c >= TK_WE_COLS;
@@ -245,9 +246,14 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
 #pragma unroll
       for (int h = 0; h < 16; ++h)
         if (__ballot_sync(0xffffffffu, we_piece == h) != 0u) we_own |= 1 << h;
-      if (we_own == 0) we_batched = false;   // this strip holds no band column
     }
+    // batched mode covers every W/E column band of the tile; a strip without band
+    // columns simply stages nothing
+    we_perrow = comm_edge && !we_batched &&
+                (a.peer[H2D_W].buf != nullptr || a.peer[H2D_E].buf != nullptr);
   }
+  const bool we_skip = we_batched;            // forward_row leaves pure W / E to flush_we
+  if (we_own == 0) we_batched = false;        // nothing to stage in this strip
 
   bool act[4] = {true, true, true, true};
   if (FROZEN) {
@@ -323,7 +329,9 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
         if (smask & 8) q[3] = fin.w;
       }
       if (EXTRAS && smask != 0) {
-        if (comm_edge) forward_row(a, r_lo + ro, j0, fin, smask, we_batched);
+        // rows outside the N/S bands have nothing to forward once W/E is batched
+        if (comm_edge && (we_perrow || r_lo + ro < a.fw || r_lo + ro >= g.rows - a.fw))
+          forward_row(a, r_lo + ro, j0, fin, smask, we_skip);
         if (a.norm != H2D_NORM_NONE) {
           const float d0 = (smask & 1) ? fin.x - cprev.x : 0.f;
           const float d1 = (smask & 2) ? fin.y - cprev.y : 0.f;
@@ -595,8 +603,10 @@ static int choose_chunk_rows(int rows, int cols, int kmax) {
   // Tasks cost about the same and the block scheduler hands them out in order,
   // so a launch takes about ceil(tasks / slots) "waves" of one task time, and a
   // task time is proportional to the rows it streams, R + 2K (K rows of pipeline
-  // fill at both ends).  Half a wave is added for the slower edge / boundary
-  // tasks.  Minimise  (ceil(waves) + 0.5) * (R + 2K)  over the chunk count.
+  // fill at both ends) plus ~8 rows of start-up.  A quarter wave is added for the
+  // slower edge / boundary tasks.  Minimise  (ceil(waves) + 0.25) * (R + 2K + 8)
+  // over the chunk count (constants fitted to sweeps on B200: 32768^2 -> R = 683,
+  // 16384^2 -> 342, 8192x32768 -> 342, 4096x32768 -> 228, all within 1 % of the best).
   // slots = SMs x resident warps (16 up to K = 5, 12 beyond: register-limited).
   // Small grids land in the latency regime (one wave): short chunks win there.
   const int wv = TK_W - 2 * round_up4(kmax);
@@ -609,7 +619,7 @@ static int choose_chunk_rows(int rows, int cols, int kmax) {
     const int R = (rows + c - 1) / c;   // equal chunks; the last one may be shorter
     if (R < r_min && c > 1) break;
     const double waves = ceil((double)((rows + R - 1) / R) * n_strips / slots);
-    const double t = (waves + 0.5) * (double)(R + 2 * kmax);
+    const double t = (waves + 0.25) * (double)(R + 2 * kmax + 8);
     if (t < best * (1.0 - 1e-9)) { best = t; best_R = R; }
   }
   return best_R;
