@@ -599,7 +599,7 @@ static int sm_count() {
   return g_sm_count;
 }
 
-static int choose_chunk_rows(int rows, int cols, int kmax) {
+static int choose_chunk_rows(int rows, int cols, int kmax, int min_waves = 1) {
   // Tasks cost about the same and the block scheduler hands them out in order,
   // so a launch takes about ceil(tasks / slots) "waves" of one task time, and a
   // task time is proportional to the rows it streams, R + 2K (K rows of pipeline
@@ -619,6 +619,10 @@ static int choose_chunk_rows(int rows, int cols, int kmax) {
     const int R = (rows + c - 1) / c;   // equal chunks; the last one may be shorter
     if (R < r_min && c > 1) break;
     const double waves = ceil((double)((rows + R - 1) / R) * n_strips / slots);
+    // With neighbours, the edge tasks (first wave) gate the neighbours' NEXT launch: keep
+    // them a small part of the launch.  (1x4 column strips at 2 waves per launch: every
+    // rank waited for its neighbours' edge tasks, 6798 instead of ~15000 GLUP/s on 4 B200.)
+    if (waves < min_waves && R > r_min) continue;
     const double t = (waves + 0.25) * (double)(R + 2 * kmax + 8);
     if (t < best * (1.0 - 1e-9)) { best = t; best_R = R; }
   }
@@ -626,8 +630,8 @@ static int choose_chunk_rows(int rows, int cols, int kmax) {
 }
 
 static void plan_counts(const h2d_tile_t* t, int kmax, int chunk_rows, int* n_chunks,
-                        int* max_tasks) {
-  int R = chunk_rows > 0 ? chunk_rows : choose_chunk_rows(t->rows, t->cols, kmax);
+                        int* max_tasks, int min_waves = 1) {
+  int R = chunk_rows > 0 ? chunk_rows : choose_chunk_rows(t->rows, t->cols, kmax, min_waves);
   int nc = (t->rows + R - 1) / R;
   if (nc < 1) nc = 1;
   *n_chunks = nc;
@@ -706,8 +710,10 @@ extern "C" {
 
 size_t h2d_plan_scratch_bytes(const h2d_tile_t* tile, int32_t kmax, int32_t chunk_rows) {
   if (!tile || kmax < 1 || kmax > TK_KMAX || tile->rows < 1 || tile->cols < 1) return 0;
-  int nc, mt;
+  int nc, mt, nc2, mt2;
   plan_counts(tile, kmax, chunk_rows, &nc, &mt);
+  plan_counts(tile, kmax, chunk_rows, &nc2, &mt2, 4);   // plans with peers use more, shorter chunks
+  if (mt2 > mt) mt = mt2;
   return scratch_layout_bytes(mt);
 }
 
@@ -771,8 +777,9 @@ h2d_plan_t* h2d_plan_create(const h2d_plan_desc_t* d) {
   p->has_peers = has_peers;
   cudaGetDevice(&p->device);
   int max_tasks = 0;
-  plan_counts(&t, d->kmax, d->chunk_rows, &p->n_chunks, &max_tasks);
-  p->chunk_rows = d->chunk_rows > 0 ? d->chunk_rows : choose_chunk_rows(t.rows, t.cols, d->kmax);
+  const int min_waves = has_peers ? 4 : 1;
+  plan_counts(&t, d->kmax, d->chunk_rows, &p->n_chunks, &max_tasks, min_waves);
+  p->chunk_rows = d->chunk_rows > 0 ? d->chunk_rows : choose_chunk_rows(t.rows, t.cols, d->kmax, min_waves);
   if (p->n_chunks == 1) p->chunk_rows = t.rows;
   p->fw = d->kmax;
   if (p->fw > t.rows) p->fw = t.rows;
