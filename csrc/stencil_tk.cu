@@ -206,7 +206,15 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
   const int r_lo = a.row_base + chunk * R;
   const int r_hi = min(r_lo + R, a.row_end);
   const int n_out = r_hi - r_lo;
-  const int jbase = strip * a.wv - a.H;  // tile-local column of lane 0, element 0
+  // The last strip is shifted left so that its valid window ends at the tile edge: its
+  // first columns are then computed twice (by it and by its left neighbour) but it OWNS
+  // (stores / reduces) only its own range [own_lo, cols).  No strip is narrow any more and,
+  // what matters for column halos, the last 32 columns always sit in ONE warp, so the east
+  // band leaves as whole 128-byte lines (half-line remote writes made every rank with a
+  // west neighbour ~2x slower: 1x4 strips of 8192 columns, last strip 16 wide).
+  const int own_lo = strip * a.wv;
+  const int vbase = (strip == a.n_strips - 1 && g.cols >= a.wv) ? g.cols - a.wv : own_lo;
+  const int jbase = vbase - a.H;         // tile-local column of lane 0, element 0
   const int j0 = jbase + lane * 4;
   const int row0 = r_lo - K;             // first input row (tile-local)
   // (A "skewed" variant in which level t consumes what level t-1 produced in the
@@ -223,7 +231,7 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
   int smask = 0;
 #pragma unroll
   for (int e = 0; e < 4; ++e)
-    if (lane_in && (j0 + e) >= 0 && (j0 + e) < g.cols) smask |= 1 << e;
+    if (lane_in && (j0 + e) >= own_lo && (j0 + e) < g.cols) smask |= 1 << e;
   const bool st_full = smask == 15;
   const bool st_part = smask != 0 && smask != 15;
 
@@ -238,7 +246,7 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
     const bool e_ok = a.peer[H2D_E].buf != nullptr && a.peer[H2D_E].halo_c >= TK_WE_COLS;
     we_batched = comm_edge && a.fw <= 8 && (g.cols & 3) == 0 && g.cols >= 2 * TK_WE_COLS && (w_ok || e_ok) &&
                  (a.peer[H2D_W].buf == nullptr || w_ok) && (a.peer[H2D_E].buf == nullptr || e_ok);
-    if (we_batched && smask == 15) {
+    if (we_batched && lane_in && j0 >= 0 && j0 + 3 < g.cols) {   // computed here, owned or not
       if (w_ok && j0 >= 0 && j0 < TK_WE_COLS) we_piece = j0 >> 2;
       if (e_ok && j0 >= g.cols - TK_WE_COLS && j0 < g.cols) we_piece = 8 + ((j0 - (g.cols - TK_WE_COLS)) >> 2);
     }
@@ -457,7 +465,7 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
     const int R = a.chunk_rows;
     const int r_lo = a.row_base + chunk * R;
     const int r_hi = min(r_lo + R, a.row_end);
-    const int jb = strip * a.wv - a.H;
+    const int jb = ((strip == a.n_strips - 1 && g.cols >= a.wv) ? g.cols - a.wv : strip * a.wv) - a.H;
     const bool frozen = (g.x0 + r_lo - K < g.ax_lo) || (g.x0 + r_hi - 1 + K > g.ax_hi) ||
                         (g.y0 + jb < g.ay_lo) || (g.y0 + jb + TK_W - 1 > g.ay_hi);
     const bool extras = XTR && (comm_edge || a.norm != H2D_NORM_NONE);
