@@ -213,7 +213,8 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
   // band leaves as whole 128-byte lines (half-line remote writes made every rank with a
   // west neighbour ~2x slower: 1x4 strips of 8192 columns, last strip 16 wide).
   const int own_lo = strip * a.wv;
-  const int vbase = (strip == a.n_strips - 1 && g.cols >= a.wv) ? g.cols - a.wv : own_lo;
+  // (rounded up to a multiple of 4: float4 stores and TMA box origins must stay 16-byte aligned)
+  const int vbase = (strip == a.n_strips - 1 && g.cols >= a.wv) ? ((g.cols - a.wv + 3) & ~3) : own_lo;
   const int jbase = vbase - a.H;         // tile-local column of lane 0, element 0
   const int j0 = jbase + lane * 4;
   const int row0 = r_lo - K;             // first input row (tile-local)
@@ -465,7 +466,7 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
     const int R = a.chunk_rows;
     const int r_lo = a.row_base + chunk * R;
     const int r_hi = min(r_lo + R, a.row_end);
-    const int jb = ((strip == a.n_strips - 1 && g.cols >= a.wv) ? g.cols - a.wv : strip * a.wv) - a.H;
+    const int jb = ((strip == a.n_strips - 1 && g.cols >= a.wv) ? ((g.cols - a.wv + 3) & ~3) : strip * a.wv) - a.H;
     const bool frozen = (g.x0 + r_lo - K < g.ax_lo) || (g.x0 + r_hi - 1 + K > g.ax_hi) ||
                         (g.y0 + jb < g.ay_lo) || (g.y0 + jb + TK_W - 1 > g.ay_hi);
     const bool extras = XTR && (comm_edge || a.norm != H2D_NORM_NONE);
