@@ -923,7 +923,8 @@ int h2d_plan_run_many(h2d_plan_t* const* plans, int n_plans, int src_parity, int
 // One k-step launch restricted to owned rows [row_base, row_end) of a single tile
 // (no peers, no norm): tasks are enumerated arithmetically, chunk c starts at
 // row_base + c * R.
-static int launch_window(h2d_plan* p, int src_parity, int k, int row_base, int row_end, cudaStream_t st) {
+static int launch_window(h2d_plan* p, int src_parity, int k, int row_base, int row_end, int chunk_rows,
+                         cudaStream_t st) {
   if (row_end <= row_base) return H2D_OK;
   tk_fn_t fn = tk_pick(k, p->desc.phys.arith, coef_is_reference(p->geo, p->desc.phys.arith), false);
   if (!fn) return h2d_fail(H2D_EINVAL, "launch_window: no kernel for k = %d", k);
@@ -933,7 +934,7 @@ static int launch_window(h2d_plan* p, int src_parity, int k, int row_base, int r
   a.g = p->geo;
   a.dst = p->desc.buf[1 - src_parity];
   a.tasks = nullptr;
-  a.chunk_rows = p->chunk_rows;
+  a.chunk_rows = chunk_rows;
   a.row_base = row_base;
   a.row_end = row_end;
   a.H = H;
@@ -967,7 +968,10 @@ int h2d_plan_solve_pipelined(h2d_plan_t* p, const float* host_in, int64_t in_pit
   const h2d_tile_t& t = p->desc.tile;
   if (in_pitch < t.cols || out_pitch < t.cols) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: host pitch < cols");
   const int rows = t.rows;
-  const int R = p->chunk_rows;
+  // windows are a few waves of tasks only: shorter chunks than whole-grid launches use
+  // (measured on B200, 32768^2: chunks of ~320 rows and blocks of ~7600 rows are best)
+  int R = p->chunk_rows;
+  while (R > 384) R = (R + 1) / 2;
   const int S = skew_rows > 0 ? skew_rows : k + 4;       // rows the processed window moves up per launch
   if (S < k + 1) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: skew %d must exceed k = %d", S, k);
   const int L = (int)((steps + k - 1) / k);              // launches ("levels") per block
@@ -1062,7 +1066,7 @@ int h2d_plan_solve_pipelined(h2d_plan_t* p, const float* host_in, int64_t in_pit
       if (lo < 0) lo = 0;
       if (hi > rows) hi = rows;
       const int kk = (e < L - 1) ? k : (int)(steps - (int64_t)(L - 1) * k);
-      if (int rc = launch_window(p, e & 1, kk, (int)lo, (int)hi, cs)) return rc;
+      if (int rc = launch_window(p, e & 1, kk, (int)lo, (int)hi, R, cs)) return rc;
     }
     // rows below b_hi - S*(L-1) now hold the final field
     int64_t fin = b_hi - (int64_t)S * (L - 1);
