@@ -717,6 +717,11 @@ static int build_task_list(h2d_plan* p, int H, TaskList* out) {
 
 extern "C" {
 
+int32_t h2d_plan_chunk_rows(const h2d_tile_t* tile, int32_t kmax, int32_t with_peers) {
+  if (!tile || kmax < 1 || kmax > TK_KMAX || tile->rows < 1 || tile->cols < 1) return 0;
+  return choose_chunk_rows(tile->rows, tile->cols, kmax, with_peers ? 4 : 1);
+}
+
 size_t h2d_plan_scratch_bytes(const h2d_tile_t* tile, int32_t kmax, int32_t chunk_rows) {
   if (!tile || kmax < 1 || kmax > TK_KMAX || tile->rows < 1 || tile->cols < 1) return 0;
   int nc, mt, nc2, mt2;

@@ -186,6 +186,9 @@ typedef struct h2d_plan_desc {
 } h2d_plan_desc_t;
 
 size_t h2d_plan_scratch_bytes(const h2d_tile_t* tile, int32_t kmax, int32_t chunk_rows);
+/* Rows per streaming task the plan would choose for this tile (pure host computation:
+ * the makespan model of DESIGN.md section 3; with_peers != 0 asks for >= 4 waves). */
+int32_t h2d_plan_chunk_rows(const h2d_tile_t* tile, int32_t kmax, int32_t with_peers);
 h2d_plan_t* h2d_plan_create(const h2d_plan_desc_t* desc);
 void h2d_plan_destroy(h2d_plan_t* plan);
 

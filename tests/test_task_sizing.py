@@ -1,0 +1,43 @@
+"""The plan's task-sizing heuristic (host-only code of libheat2d_cuda.so; runs without a GPU,
+where the SM count falls back to 148)."""
+import ctypes as C
+
+import pytest
+
+from heat2d_b200 import _native as N
+
+
+def chunk_rows(rows, cols, k=8, peers=False):
+    lib = N.cuda()
+    t = N.make_tile(rows, cols, 0, 0, rows, cols, 8, 32, (cols + 64 + 31) // 32 * 32)
+    return lib.h2d_plan_chunk_rows(C.byref(t), k, int(peers))
+
+
+def waves(rows, cols, R, k=8):
+    wv = 128 - 2 * ((k + 3) // 4 * 4)
+    ns = -(-cols // wv)
+    return -(-rows // R) * ns / (148 * (16 if k <= 5 else 12))
+
+
+@pytest.mark.parametrize("rows,cols,lo,hi", [(32768, 32768, 450, 1024), (16384, 16384, 256, 512),
+                                              (8192, 32768, 300, 400), (4096, 32768, 200, 260)])
+def test_large_tiles_get_the_measured_best_chunks(rows, cols, lo, hi):
+    # fitted to sweeps on B200 (profiles/ROOFLINE.md): within 1 % of the best chunk size
+    R = chunk_rows(rows, cols)
+    assert lo <= R <= hi, R
+    w = waves(rows, cols, R)
+    assert w <= round(w) + 1e-9 or w - int(w) > 0.9   # just under a whole number of waves
+
+
+def test_small_grids_use_short_chunks():
+    assert chunk_rows(640, 512) == 8        # one wave anyway: shortest tasks win (latency regime)
+    assert chunk_rows(10, 10) == 10         # a single chunk
+    assert chunk_rows(2560, 2048) <= 32
+
+
+def test_plans_with_peers_keep_edge_tasks_short():
+    # >= 4 waves per launch: the edge tasks (first wave) gate the neighbours' next launch
+    for rows, cols in [(32768, 8192), (4096, 32768), (8192, 16384)]:
+        R = chunk_rows(rows, cols, peers=True)
+        assert waves(rows, cols, R) > 3.0
+        assert R <= chunk_rows(rows, cols, peers=False)
