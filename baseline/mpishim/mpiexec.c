@@ -15,6 +15,7 @@
 #include <sys/socket.h>
 #include <sys/types.h>
 #include <sys/wait.h>
+#include <time.h>
 #include <unistd.h>
 
 int main(int argc, char** argv) {
@@ -56,16 +57,31 @@ int main(int argc, char** argv) {
     }
   }
   for (int i = 0; i < n; ++i) for (int j = 0; j < n; ++j) if (fd[i][j] >= 0) close(fd[i][j]);
-  int rc = 0, left = n;
+  /* The first failing rank decides the exit code.  The others get a short grace
+   * period to finish what they were printing (a program may report its error on
+   * one rank while another trips over the same misconfiguration a moment
+   * earlier), then SIGTERM. */
+  int rc = 0, left = n, killed = 0;
+  struct timespec t_fail = {0, 0};
+  char* done = calloc((size_t)n, 1);
   while (left > 0) {
-    int st; pid_t p = wait(&st);
+    int st; pid_t p = waitpid(-1, &st, rc != 0 && !killed ? WNOHANG : 0);
     if (p < 0) { if (errno == EINTR) continue; break; }
-    --left;
-    int code = WIFEXITED(st) ? WEXITSTATUS(st) : 128 + WTERMSIG(st);
-    if (code != 0 && rc == 0) {
-      rc = code;
-      for (int r = 0; r < n; ++r) if (pid[r] != p) kill(pid[r], SIGTERM);
+    if (p == 0) {  /* a rank failed, nobody else has exited yet */
+      struct timespec now; clock_gettime(CLOCK_MONOTONIC, &now);
+      double waited = (double)(now.tv_sec - t_fail.tv_sec) + 1e-9 * (double)(now.tv_nsec - t_fail.tv_nsec);
+      if (waited > 0.25) {
+        for (int r = 0; r < n; ++r) if (!done[r]) kill(pid[r], SIGTERM);
+        killed = 1;
+      } else {
+        struct timespec nap = {0, 5 * 1000 * 1000}; nanosleep(&nap, NULL);
+      }
+      continue;
     }
+    --left;
+    for (int r = 0; r < n; ++r) if (pid[r] == p) done[r] = 1;
+    int code = WIFEXITED(st) ? WEXITSTATUS(st) : 128 + WTERMSIG(st);
+    if (code != 0 && rc == 0) { rc = code; clock_gettime(CLOCK_MONOTONIC, &t_fail); }
   }
   return rc;
 }

@@ -228,8 +228,7 @@ def main():
             "halo_wait_us_rank0": (solver.halo_wait_stats()[0] if hasattr(solver, "halo_wait_stats") else None),
             "baseline_ref": "10.1 GLUP/s = best published reference number (grad1612 MPI, 2560x2048, 160 ranks, "
                             "Report.pdf p21); published CUDA number is 0.669 GLUP/s",
-            "roofline": {"hbm_gbs_measured": _peaks().get("hbm_gbs"),
-                         "k1_hbm_bound_glups_per_gpu": (_peaks().get("hbm_gbs") or 0) / 8.0},
+            "roofline": _roofline(glups, nx, ny, px, py, k, a.chunk_rows),
         }
         if e2e is not None:
             out["e2e"] = e2e
@@ -241,6 +240,25 @@ def main():
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+def _roofline(glups, nx, ny, px, py, k, chunk_rows):
+    """Achieved fraction of the three-roof bound (fp32 pipe / HBM / NVLink), whole job."""
+    out = {"hbm_gbs_measured": _peaks().get("hbm_gbs"),
+           "k1_hbm_bound_glups_per_gpu": (_peaks().get("hbm_gbs") or 0) / 8.0}
+    try:
+        import ctypes
+        from heat2d_b200 import _native as N
+        from heat2d_b200.utils.perfmodel import roofline_fraction
+        rows, cols = -(-nx // px), -(-ny // py)
+        if chunk_rows <= 0:
+            t = N.Tile(nx, ny, 0, 0, rows, cols, max(k, 8), 32, cols + 64)
+            chunk_rows = int(N.cuda().h2d_plan_chunk_rows(ctypes.byref(t), k, int(px * py > 1)))
+        out.update(roofline_fraction(glups, nx, ny, px, py, k, chunk_rows))
+        out["chunk_rows"] = chunk_rows
+    except Exception as e:  # noqa: BLE001 - the model is a report, never a reason to lose the bench line
+        out["model_error"] = str(e)[:120]
+    return out
 
 
 def _peaks():

@@ -213,6 +213,10 @@ def main(argv=None) -> int:
                 hbm = json.load(f).get("hbm_gbs")
             if hbm and cfg.backend not in ("cpu",):
                 rec["pct_of_k1_hbm_roofline"] = 100.0 * res.glups / (hbm / 8.0 * max(world, 1))
+            if cfg.backend in ("fused", "single"):
+                from .utils.perfmodel import roofline_fraction
+                rec["roofline"] = roofline_fraction(res.glups, cfg.nx, cfg.ny, cfg.px, cfg.py, max(cfg.k, 1),
+                                                    cfg.chunk_rows)
         except Exception:  # noqa: BLE001
             pass
         os.makedirs(cfg.out_dir, exist_ok=True)

@@ -22,6 +22,7 @@ from .. import _native as N
 from ..config import HeatConfig, Launch, make_schedule
 from ..ops import kernels as K
 from ..parallel.decomp import Decomposition, OPPOSITE, TileSpec
+from ..utils.timing import nvtx_range
 
 COL_MARGIN = 32  # floats; keeps owned column 0 128-byte aligned and >= roundup4(KMAX)
 
@@ -277,11 +278,12 @@ class Heat2DSolver:
     def run(self, steps: Optional[int] = None) -> RunResult:
         cfg = self.cfg
         steps = cfg.steps if steps is None else steps
-        if cfg.backend == "resident":
-            return self._run_resident(steps)
-        if cfg.backend == "plain":
-            return self._run_plain(steps)
-        return self._run_fused(steps)
+        with nvtx_range(f"heat2d.run[{cfg.backend} k={cfg.k} steps={steps}]"):
+            if cfg.backend == "resident":
+                return self._run_resident(steps)
+            if cfg.backend == "plain":
+                return self._run_plain(steps)
+            return self._run_fused(steps)
 
     def _run_fused(self, steps: int) -> RunResult:
         """Queue the whole run without ever synchronising with the device.

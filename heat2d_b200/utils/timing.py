@@ -1,12 +1,41 @@
 """Per-phase timers for the drivers (CLI, bench): wall clock on the host and, when a
 device is given, CUDA events on the current stream.  The reference times exactly one
 window (barrier .. end of the step loop, ``grad1612_mpi_heat.c:206-207,277-280``); the
-phases here show what surrounds it (init, dumps, gather)."""
+phases here show what surrounds it (init, dumps, gather).
+
+With ``H2D_NVTX=1`` in the environment every phase (and every ``nvtx_range``) is also an
+NVTX range, so a timeline tool shows the same names.  The reference's tracing was
+link-time mpiP interposition (``Report.pdf`` p34-37); it has no in-source hooks."""
 from __future__ import annotations
 
+import os
 import time
 from contextlib import contextmanager
 from typing import Dict, Optional
+
+
+def nvtx_enabled() -> bool:
+    return os.environ.get("H2D_NVTX", "0") not in ("", "0")
+
+
+@contextmanager
+def nvtx_range(name: str):
+    """NVTX range around a block when H2D_NVTX=1 and CUDA is usable; otherwise free."""
+    pushed = False
+    if nvtx_enabled():
+        try:
+            import torch
+            if torch.cuda.is_available():
+                torch.cuda.nvtx.range_push(name)
+                pushed = True
+        except Exception:  # NVTX is a convenience, never a reason to fail a run
+            pushed = False
+    try:
+        yield
+    finally:
+        if pushed:
+            import torch
+            torch.cuda.nvtx.range_pop()
 
 
 class PhaseTimer:
@@ -25,7 +54,8 @@ class PhaseTimer:
                 ev0.record(torch.cuda.current_stream(self.device))
         t0 = time.perf_counter()
         try:
-            yield self
+            with nvtx_range(name):
+                yield self
         finally:
             if ev1 is not None:
                 ev1.record(torch.cuda.current_stream(self.device))
