@@ -48,6 +48,8 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("-k", type=int, help="time steps per launch / halo exchange (1..8)")
     ap.add_argument("--backend", choices=BACKENDS)
     ap.add_argument("--chunk-rows", type=int)
+    ap.add_argument("--dataflow", action="store_true",
+                    help="single tile, no convergence: all sweeps in one dataflow launch")
     ap.add_argument("--threads", type=int, help="NUMTHREADS (cpu backend)")
     ap.add_argument("--no-uneven", action="store_true", help="insist on exact divisibility (grad1612_mpi_heat.c:60)")
     ap.add_argument("--restart", help="raw fp32 nx*ny file (final_binary.dat) to start from")
@@ -77,6 +79,8 @@ def config_from_args(a) -> HeatConfig:
         over["uneven"] = False
     if a.debug:
         over["debug"] = True
+    if getattr(a, "dataflow", False):
+        over["dataflow"] = True
     if a.ref_conv_bug:
         over["ref_conv_bug"] = True
     cfg = cfg.replace(**over)

@@ -55,6 +55,8 @@ class HeatConfig:
     start_step: int = 0
     ref_conv_bug: bool = False   # replay the stale-`i` predicate of grad1612_mpi_heat.c:263
     spin_timeout_s: float = 10.0
+    dataflow: bool = False       # one dataflow launch per run of equal-k sweeps
+                                 # (single tile, no convergence test; h2d_plan_run_dataflow)
 
     def validate(self, world_size: Optional[int] = None) -> "HeatConfig":
         if self.nx < 1 or self.ny < 1:

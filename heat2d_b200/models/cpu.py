@@ -17,14 +17,15 @@ from ..ops import kernels as K
 
 
 class CpuResult:
-    def __init__(self, steps_done, iterations, converged, last_norm, elapsed_s, nx, ny):
+    def __init__(self, steps_done, iterations, converged, last_norm, elapsed_s, nx, ny, steps_run=None):
         self.steps_done, self.iterations, self.converged = steps_done, iterations, converged
+        self.steps_run = steps_done if steps_run is None else steps_run   # updates applied by this call
         self.last_norm, self.elapsed_s, self.nx, self.ny = last_norm, elapsed_s, nx, ny
         self.launches, self.checks = 0, 0
 
     @property
     def glups(self) -> float:
-        return self.nx * self.ny * self.steps_done / self.elapsed_s / 1e9 if self.elapsed_s > 0 else float("nan")
+        return self.nx * self.ny * self.steps_run / self.elapsed_s / 1e9 if self.elapsed_s > 0 else float("nan")
 
 
 class CpuSolver:
@@ -51,7 +52,7 @@ class CpuSolver:
         el = time.perf_counter() - t0
         conv = cfg.conv and done < steps
         self.steps_done += done
-        return CpuResult(self.steps_done, self.steps_done, conv, last, el, cfg.nx, cfg.ny)
+        return CpuResult(self.steps_done, self.steps_done, conv, last, el, cfg.nx, cfg.ny, done)
 
     def gather(self):
         import torch

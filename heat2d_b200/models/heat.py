@@ -110,12 +110,15 @@ class RunResult:
     checks: int
     nx: int
     ny: int
+    steps_run: int = -1        # updates applied by THIS call (steps_done also counts earlier calls / start_step)
 
     @property
     def glups(self) -> float:
+        """Throughput of this call: grid points x updates applied by it / its device time."""
         if self.elapsed_s <= 0:
             return float("nan")
-        return self.nx * self.ny * max(self.steps_done, 0) / self.elapsed_s / 1e9
+        n = self.steps_run if self.steps_run >= 0 else self.steps_done
+        return self.nx * self.ny * max(n, 0) / self.elapsed_s / 1e9
 
 
 class TileEngine:
@@ -307,6 +310,7 @@ class Heat2DSolver:
         records = {}   # seq -> (parity before, k, first_step, epoch of the check launch, launches so far)
         launches = 0
         parity, epoch, done = self.parity, self.epoch, self.steps_done
+        done0 = done
         with torch.cuda.device(self.device):
             if cfg.conv:
                 for e in self.engines:
@@ -320,9 +324,13 @@ class Heat2DSolver:
                     while j < len(sched) and sched[j].k == L.k and not (sched[j].check and cfg.conv):
                         j += 1
                     n = j - i
-                    K.Plan.run_many(plans, parity, L.k, n, epoch + 1, ctls if cfg.conv else None)
+                    if cfg.dataflow and len(plans) == 1 and self.world == 1 and not cfg.conv and n > 1:
+                        plans[0].run_dataflow(parity, L.k, n)
+                        launches += 1
+                    else:
+                        K.Plan.run_many(plans, parity, L.k, n, epoch + 1, ctls if cfg.conv else None)
+                        launches += n * len(plans)
                     epoch += n
-                    launches += n * len(plans)
                     parity ^= n & 1
                     done += n * L.k
                     i = j
@@ -370,7 +378,7 @@ class Heat2DSolver:
         if iterations is None:
             iterations = self.steps_done
         return RunResult(self.steps_done, iterations, converged, last_norm, elapsed, launches, checks,
-                         cfg.nx, cfg.ny)
+                         cfg.nx, cfg.ny, self.steps_done - done0)
 
     def solve_pipelined(self, host_in: torch.Tensor, host_out: torch.Tensor, steps: Optional[int] = None,
                         block_rows: int = 0, skew_rows: int = 0) -> RunResult:
@@ -394,7 +402,7 @@ class Heat2DSolver:
             ev1.synchronize()
         self.steps_done = cfg.start_step + steps
         return RunResult(self.steps_done, self.steps_done, False, float("nan"), ev0.elapsed_time(ev1) / 1e3,
-                         plan.launch_count - l0, 0, cfg.nx, cfg.ny)
+                         plan.launch_count - l0, 0, cfg.nx, cfg.ny, steps)
 
     def _run_plain(self, steps: int) -> RunResult:
         """Plain one-step kernel + standalone norm kernel, host-side decision (the
@@ -404,6 +412,7 @@ class Heat2DSolver:
         ev0 = torch.cuda.Event(enable_timing=True)
         ev1 = torch.cuda.Event(enable_timing=True)
         converged, last_norm, checks, launches, iterations = False, float("nan"), 0, 0, None
+        done0 = self.steps_done
         with torch.cuda.device(self.device):
             ev0.record()
             for s in range(self.steps_done, self.steps_done + steps):
@@ -424,7 +433,7 @@ class Heat2DSolver:
         if iterations is None:
             iterations = self.steps_done
         return RunResult(self.steps_done, iterations, converged, last_norm, ev0.elapsed_time(ev1) / 1e3,
-                         launches, checks, cfg.nx, cfg.ny)
+                         launches, checks, cfg.nx, cfg.ny, self.steps_done - done0)
 
     def _run_resident(self, steps: int) -> RunResult:
         cfg = self.cfg
@@ -441,15 +450,17 @@ class Heat2DSolver:
         self.parity ^= 1
         self.steps_done += steps
         return RunResult(self.steps_done, self.steps_done, False, float("nan"),
-                         ev0.elapsed_time(ev1) / 1e3, 1, 0, cfg.nx, cfg.ny)
+                         ev0.elapsed_time(ev1) / 1e3, 1, 0, cfg.nx, cfg.ny, steps)
 
     def _check_faults(self):
         for e in self.engines:
             code = e.fault()
             if code:
                 raise RuntimeError(
-                    f"rank {e.rank}: flag wait timed out (code {code}: "
-                    f"{'direction ' + N.DIRS[code - 1] if code < 100 else 'norm slot of rank ' + str(code - 100)})")
+                    f"rank {e.rank}: flag wait timed out (code {code}: " + (
+                        "task dependency inside the dataflow launch" if code == 50 else
+                        "direction " + N.DIRS[code - 1] if code < 50 else
+                        "norm slot of rank " + str(code - 100)) + ")")
 
     # ----------------------------------------------------------------- output
     def gather(self, out: Optional[torch.Tensor] = None) -> torch.Tensor:

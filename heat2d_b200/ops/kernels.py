@@ -217,6 +217,14 @@ class Plan:
             N.check(lib, lib.h2d_plan_run_many(arr, len(plans), src_parity, k, n_launches,
                                                epoch0 & 0xFFFFFFFF, ctl, _stream_ptr(plans[0].device)))
 
+    def run_dataflow(self, src_parity: int, k: int, n_epochs: int) -> int:
+        """`n_epochs` k-step sweeps in one dataflow launch (h2d_plan_run_dataflow);
+        returns the parity of the buffer that holds the result."""
+        with torch.cuda.device(self.device):
+            N.check(self._lib, self._lib.h2d_plan_run_dataflow(self._h, src_parity, k, n_epochs,
+                                                                 _stream_ptr(self.device)))
+        return src_parity ^ (n_epochs & 1)
+
     def solve_pipelined(self, host_in: torch.Tensor, host_out: torch.Tensor, steps: int, k: int,
                         block_rows: int = 0, skew_rows: int = 0) -> int:
         """Upload `host_in`, advance `steps` steps, download into `host_out`, overlapped

@@ -357,6 +357,7 @@ class HaloExchangeSolver:
             ev0.record()
         t0 = time.perf_counter()
         converged, last, checks, iterations = False, float("nan"), 0, None
+        done0 = self.steps_done
         for s in range(self.steps_done, self.steps_done + steps):
             if self.world > 1:
                 self._exchange()
@@ -382,7 +383,7 @@ class HaloExchangeSolver:
         if iterations is None:
             iterations = self.steps_done
         return RunResult(self.steps_done, iterations, converged, last, el, self.kernel_launches, checks,
-                         cfg.nx, cfg.ny)
+                         cfg.nx, cfg.ny, self.steps_done - done0)
 
     def gather(self, out: Optional[torch.Tensor] = None, dst: int = 0):
         cfg = self.cfg

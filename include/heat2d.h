@@ -221,6 +221,16 @@ int h2d_plan_launch_ex(h2d_plan_t* plan, int src_parity, int k, uint32_t epoch, 
 int h2d_plan_run_many(h2d_plan_t* const* plans, int n_plans, int src_parity, int k, int n_launches,
                       uint32_t epoch0, const uint32_t* const* ctls /* per plan, or NULL */, void* stream);
 
+/* `n_epochs` k-step sweeps in ONE launch (single-tile plans, no norm): a grid with one
+ * warp per (epoch, task); warps draw tickets in that order and start a task as soon as the tasks
+ * of the previous epoch that it reads from / writes over have finished, so the machine
+ * never drains between sweeps.  Result parity as with h2d_plan_run_many:
+ * src_parity ^ (n_epochs & 1).  The first call allocates one counter per task (later
+ * calls with the same or a smaller k reuse them).  A dependency that does not arrive
+ * within the plan's spin timeout sets the fault word to 50 and the kernel winds down.
+ * The reference launches once per time step (grad1612_cuda_heat.cu:82-85).          */
+int h2d_plan_run_dataflow(h2d_plan_t* plan, int src_parity, int k, int n_epochs, void* stream);
+
 /* Upload, solve, download — overlapped.  For a single-tile plan: copies the nx x ny
  * field `host_in` (pinned host memory, `in_pitch` floats per row) into buf[0], advances
  * it `steps` steps in launches of k, and copies the result to `host_out`, with the
@@ -244,7 +254,8 @@ int64_t h2d_plan_launch_count(const h2d_plan_t* plan);
  * with norm != NONE has completed). */
 float* h2d_plan_norm_ptr(h2d_plan_t* plan);
 /* Device address of the watchdog word: non-zero after a flag wait timed out
- * (value = 1 + direction that stalled). */
+ * (value = 1 + direction that stalled; 50 = a task dependency inside
+ * h2d_plan_run_dataflow; 100 + rank = a norm slot). */
 uint32_t* h2d_plan_fault_ptr(h2d_plan_t* plan);
 /* Device address of two 64-bit counters: [0] nanoseconds edge tasks spent blocked on a
  * neighbour's epoch flag, [1] how many such waits blocked at all — the in-kernel
