@@ -124,7 +124,6 @@ def main(argv=None) -> int:
         print("Quitting...", file=sys.stderr)
         return 1
 
-    import numpy as np
     import torch
     rank, world = 0, 1
     solver = None

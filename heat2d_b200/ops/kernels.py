@@ -6,7 +6,7 @@ is no PyTorch fallback — a missing ``libheat2d_cuda.so`` raises.
 from __future__ import annotations
 
 import ctypes as C
-from typing import Optional, Sequence
+from typing import Optional
 
 import numpy as np
 import torch

@@ -30,7 +30,7 @@ import torch
 import torch.distributed as dist
 
 from .. import _native as N
-from ..config import HeatConfig, Launch, make_schedule
+from ..config import HeatConfig
 from ..models.heat import (Heat2DSolver, RunResult, TileEngine, TileField, padded_bytes,
                            padded_geometry, tensor_from_ptr)
 from ..ops import kernels as K

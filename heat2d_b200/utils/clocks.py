@@ -9,7 +9,6 @@ import shutil
 import statistics
 import subprocess
 import threading
-import time
 from typing import List, Optional
 
 QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"

@@ -11,7 +11,7 @@ from __future__ import annotations
 import os
 import time
 from contextlib import contextmanager
-from typing import Dict, Optional
+from typing import Dict
 
 
 def nvtx_enabled() -> bool:

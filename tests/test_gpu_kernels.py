@@ -8,7 +8,7 @@ import torch
 
 from heat2d_b200 import _native as N
 from heat2d_b200.config import HeatConfig
-from heat2d_b200.models.heat import Heat2DSolver, TileField, padded_geometry
+from heat2d_b200.models.heat import Heat2DSolver, TileField
 from heat2d_b200.ops import kernels as K
 from heat2d_b200.parallel.decomp import Decomposition
 
