@@ -239,11 +239,14 @@ int h2d_cuda_device_info(int device, char* out, size_t cap) {
   int clusters = 0;
   cudaDeviceGetAttribute(&clusters, cudaDevAttrClusterLaunch, device);
   snprintf(out, cap,
-           "%s: %d.%d\nGlobal memory: %zu MB\nShared memory per block (opt-in): %zu KB\n"
-           "Registers per block: %d\nWarp size: %d\nMax threads per block: %d\n"
+           "%s: %d.%d\nGlobal memory: %zu MB\nShared memory per block: %zu KB (opt-in %zu KB)\n"
+           "Constant memory: %zu KB\nRegisters per block: %d\nWarp size: %d\nMax threads per block: %d\n"
+           "Max block dimensions: [%d, %d, %d]\nMax grid dimensions: [%d, %d, %d]\n"
            "SMs: %d\nL2: %d MB\nCluster launch: %d\n",
-           p.name, p.major, p.minor, p.totalGlobalMem >> 20, p.sharedMemPerBlockOptin >> 10,
-           p.regsPerBlock, p.warpSize, p.maxThreadsPerBlock, p.multiProcessorCount,
+           p.name, p.major, p.minor, p.totalGlobalMem >> 20, p.sharedMemPerBlock >> 10,
+           p.sharedMemPerBlockOptin >> 10, p.totalConstMem >> 10, p.regsPerBlock, p.warpSize,
+           p.maxThreadsPerBlock, p.maxThreadsDim[0], p.maxThreadsDim[1], p.maxThreadsDim[2],
+           p.maxGridSize[0], p.maxGridSize[1], p.maxGridSize[2], p.multiProcessorCount,
            p.l2CacheSize >> 20, clusters);
   return H2D_OK;
 }

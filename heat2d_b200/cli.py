@@ -96,7 +96,8 @@ def _banner(cfg: HeatConfig, world: int, style: str):
     elif style == "grad1612_cuda":
         print(f"Problem size: {cfg.nx}x{cfg.ny}\nAmount of iterations: {cfg.steps}")
     else:
-        print(f"Starting with {world} processes\nProblem size:{cfg.nx}x{cfg.ny}\n"
+        threads = f" and {cfg.threads} threads" if style == "grad1612_hybrid" else ""   # grad1612_hybrid_heat.c:70
+        print(f"Starting with {world} processes{threads}\nProblem size:{cfg.nx}x{cfg.ny}\n"
               f"Each process will take: {cfg.nx // cfg.px}x{cfg.ny // cfg.py}\nAmount of iterations: {cfg.steps}")
         if cfg.conv:
             print(f"Check for convergence every {cfg.interval} iterations")
@@ -154,13 +155,19 @@ def main(argv=None) -> int:
     if cfg.debug:
         from .parallel.decomp import Decomposition
         dec = Decomposition(cfg.nx, cfg.ny, cfg.px, cfg.py, cfg.uneven)
-        t = dec.tile(rank if world > 1 else 0)
-        nb = t.neighbours
-        print(f"I am {rank} and my neighbors are North={nb['N']}, South={nb['S']}, East={nb['E']}, "
-              f"West={nb['W']} (Running on {os.uname().nodename})")
+        # grad1612_mpi_heat.c:170-175; a missing neighbour prints as MPI_PROC_NULL, which is
+        # -2 in Open MPI and in the shim under baseline/mpishim.  One process that emulates
+        # P x Q tiles speaks for all of them.
+        null = lambda q: -2 if q is None else q
+        for t in (dec.tiles if world == 1 else [dec.tile(rank)]):
+            nb = t.neighbours
+            print(f"I am {t.rank} and my neighbors are North={null(nb['N'])}, South={null(nb['S'])}, "
+                  f"East={null(nb['E'])}, West={null(nb['W'])} (Running on {os.uname().nodename})")
         if rank == 0 and torch.cuda.is_available():
+            # every visible device, as detailsGPU() does (grad1612_cuda_heat.cu:24-37)
             from .ops import kernels as K
-            print(K.device_info(torch.cuda.current_device()))
+            for dev in range(torch.cuda.device_count()):
+                print(K.device_info(dev))
 
     with timer.phase("init"):
         if cfg.restart:
@@ -191,6 +198,16 @@ def main(argv=None) -> int:
               else "Initializing grid and writing initial.dat file...")
     with timer.phase("dump_initial"):
         write("initial")
+    if style == "mpi_heat2Dn" and rank == 0:
+        # The master's assignment log (mpi_heat2Dn.c:113-114) and the workers' start line
+        # (:173).  Workers are numbered from 1 there (task 0 is the idle master); NONE = 0.
+        from .parallel.decomp import split
+        nw = cfg.px * cfg.py
+        for i, (off, rows) in enumerate(split(cfg.nx, cfg.px), start=1):
+            left, right = (i - 1 if i > 1 else 0), (i + 1 if i < nw else 0)
+            print(f"Sent to task {i}: rows= {rows} offset= {off} left= {left} right= {right}")
+        for i in range(1, nw + 1):
+            print(f"Task {i} received work. Beginning time steps...")
     with timer.phase("run"):
         res = solver.run()
     if rank == 0:

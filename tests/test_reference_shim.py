@@ -66,6 +66,42 @@ def test_given_program_any_worker_count(tmp_path, workers):
     assert (tmp_path / "final.dat").read_bytes() == (tmp_path / "ours.dat").read_bytes()
 
 
+def test_cli_prints_the_masters_log_of_the_given_program(tmp_path, capsys):
+    """Same lines as the reference's stdout (mpi_heat2Dn.c:79-83,113-114,129,173), order aside:
+    the reference's ranks print concurrently."""
+    from heat2d_b200 import cli
+    exe = rb.build_mpi("mpi_heat2Dn", {"NXPROB": 50, "NYPROB": 37, "STEPS": 60}, "-O2")
+    ref_out, _ = rb.run_mpi(exe, 6, tmp_path)
+    capsys.readouterr()
+    rc = cli.main(["--preset", "mpi_heat2Dn", "--backend", "cpu", "--nx", "50", "--ny", "37", "--steps", "60",
+                   "--px", "5", "--dump", "prtdat", "--out-dir", str(tmp_path / "ours")])
+    assert rc == 0
+    ours = capsys.readouterr().out.splitlines()
+    keep = ("Starting mpi_heat2D", "Grid size", "Initializing grid", "Sent to task", "Task ", "Writing final.dat")
+    pick = lambda lines: sorted(l for l in lines if l.startswith(keep))
+    assert pick(ours) == pick(ref_out.splitlines())
+    assert len(pick(ours)) == 4 + 2 * 5
+    assert (tmp_path / "ours" / "final.dat").read_bytes() == (tmp_path / "final.dat").read_bytes()
+
+
+def test_cli_prints_the_banner_and_debug_lines_of_grad1612_mpi(tmp_path, capsys):
+    """grad1612_mpi_heat.c:66-69 (banner), :170-175 (DEBUG neighbours), :284-287 (result lines)."""
+    from heat2d_b200 import cli
+    defs = {"NXPROB": 12, "NYPROB": 16, "STEPS": 30, "GRIDX": 2, "GRIDY": 2, "DEBUG": 1}
+    ref_out, _ = rb.run_mpi(rb.build_mpi("grad1612_mpi", defs, "-O2"), 4, tmp_path)
+    capsys.readouterr()
+    rc = cli.main(["--preset", "grad1612_mpi", "--backend", "cpu", "--nx", "12", "--ny", "16", "--steps", "30",
+                   "--px", "2", "--py", "2", "--debug", "--dump", "rowmajor,binary",
+                   "--out-dir", str(tmp_path / "ours")])
+    assert rc == 0
+    ours = capsys.readouterr().out.splitlines()
+    drop = ("Elapsed time", "Exiting after")          # timing differs; the iteration line is checked below
+    pick = lambda lines: sorted(l for l in lines if l.strip() and not l.startswith(drop) and "GLUP/s" not in l)
+    assert pick(ours) == pick(ref_out.splitlines())
+    assert [l for l in ours if l.startswith("Exiting after")] == \
+           [l for l in ref_out.splitlines() if l.startswith("Exiting after")]
+
+
 def test_given_program_rejects_bad_worker_count(tmp_path):
     exe = rb.build_mpi("mpi_heat2Dn", {"NXPROB": 10, "NYPROB": 10, "STEPS": 10}, "-O2")
     with pytest.raises(RuntimeError, match="number of tasks must be between 4 and 9"):
@@ -128,3 +164,19 @@ def test_grad1612_hybrid_runs_on_the_shim_and_matches(tmp_path):
     s = CpuSolver(cfg).initialize()
     s.run()
     assert np.array_equal(D.read_binary(str(tmp_path / "final_binary.dat"), 24, 20), s.u)
+
+
+def test_cli_prints_the_banner_of_grad1612_hybrid(tmp_path, capsys):
+    """grad1612_hybrid_heat.c:70-72: process AND thread count, convergence line (its default)."""
+    from heat2d_b200 import cli
+    defs = {"NXPROB": 24, "NYPROB": 20, "STEPS": 40, "NUMTHREADS": 2}
+    ref_out, _ = rb.run_mpi(rb.build_mpi("grad1612_hybrid", defs, "-O2"), 1, tmp_path)
+    capsys.readouterr()
+    rc = cli.main(["--preset", "grad1612_hybrid", "--backend", "cpu", "--nx", "24", "--ny", "20", "--steps", "40",
+                   "--threads", "2", "--dump", "rowmajor,binary", "--out-dir", str(tmp_path / "ours")])
+    assert rc == 0
+    ours = capsys.readouterr().out.splitlines()
+    head = lambda lines: [l for l in lines if l.startswith(("Starting with", "Problem size", "Each process",
+                                                            "Amount of", "Check for", "Writing"))]
+    assert head(ours) == head(ref_out.splitlines())
+    assert "Starting with 1 processes and 2 threads" in ours
