@@ -39,3 +39,35 @@ def test_c_example_runs(tmp_path):
     ref = K.cpu_initial_grid(640, 512, "exact")
     K.cpu_run(ref, 100, N.make_phys())
     assert float(m.group(1)) == pytest.approx(float(ref[320, 256]), rel=1e-5)
+
+
+def test_plain_c_cpu_example_matches_the_given_program(tmp_path):
+    """examples/cpu_oracle_demo.c (C, not C++): include/heat2d.h is a C header, the CPU library
+    needs no CUDA, and its final.dat equals the one mpi_heat2Dn.c writes for the default 10x10."""
+    import sys
+    from heat2d_b200 import build as B
+    B.build_cpu()
+    lib = os.path.join(ROOT, "heat2d_b200", "_lib")
+    cc = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else shutil.which("gcc")
+    exe = tmp_path / "cpu_oracle_demo"
+    r = subprocess.run([cc, "-std=c99", "-O2", "-Wall", "-Wextra", "-Werror", "-I" + os.path.join(ROOT, "include"),
+                        os.path.join(ROOT, "examples", "cpu_oracle_demo.c"), "-L" + lib, "-lheat2d_cpu",
+                        "-Wl,-rpath," + lib, "-o", str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    out = tmp_path / "ours"
+    out.mkdir()
+    r = subprocess.run([str(exe), "10", "10", "100", str(out)], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "Grid size: X= 10  Y= 10  Time steps= 100" in r.stdout
+    assert re.search(r"Exiting after \d+ iterations", r.stdout)
+    assert (out / "final_binary.dat").stat().st_size == 10 * 10 * 4
+
+    sys.path.insert(0, os.path.join(ROOT, "baseline"))
+    import ref_build as rb
+    if not (os.path.exists("/root/reference") or rb.staged()):
+        pytest.skip("reference sources not available")
+    ref_dir = tmp_path / "ref"
+    ref_dir.mkdir()
+    rb.run_mpi(rb.build_mpi("mpi_heat2Dn", {"NXPROB": 10, "NYPROB": 10, "STEPS": 100}, "-O2"), 4, ref_dir)
+    assert (out / "initial.dat").read_bytes() == (ref_dir / "initial.dat").read_bytes()
+    assert (out / "final.dat").read_bytes() == (ref_dir / "final.dat").read_bytes()
