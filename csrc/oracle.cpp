@@ -41,8 +41,11 @@ inline Coef make_coef(const h2d_phys_t* p) {
 
 // One grid point.  xm/xp: neighbours in the slow (row) index, ym/yp: in the
 // contiguous index.
+// always_inline: the row kernels below are compiled once per instruction set, and the
+// fma / conversion code must be generated for the set of the kernel it ends up in.
 template <int ARITH>
-inline float point(float c, float xm, float xp, float ym, float yp, const Coef& k) {
+__attribute__((always_inline)) inline float point(float c, float xm, float xp, float ym, float yp,
+                                                  const Coef& k) {
   float ew = xp + xm;  // fl32, as the C expression `u[i+1][j] + u[i-1][j]`
   float ns = yp + ym;
   if (ARITH == H2D_ARITH_FP32) {
@@ -76,32 +79,70 @@ inline Active active_range(int32_t nx, int32_t ny, int boundary) {
   return {0, nx - 1, 0, ny - 1};
 }
 
+// ---------------------------------------------------------------- row kernels
+// One output row, columns [y0, y1]: every operand is a plain array read (rows outside
+// the grid are a row of zeros, columns outside it are handled by the caller), so the loop
+// has no branches and vectorises.  The arithmetic is point<ARITH>() element by element —
+// vector instructions round each lane exactly like the scalar ones — and -ffp-contract=off
+// still forbids fusing in the strict variant.  Each kernel is compiled three times
+// (baseline x86-64, x86-64-v3 = AVX2 + FMA, x86-64-v4 = AVX-512) and the loader picks one at run time
+// (target_clones): the library is built on one box and runs on another.
+//
+// The reference's sweeps are the scalar loops of mpi_heat2Dn.c:225-237 and
+// grad1612_mpi_heat.c:239-259; gcc -O3 vectorises those too, which is why its single
+// rank (0.50 GLUP/s on this box's CPU) used to beat this oracle (0.19) before this rewrite.
+#if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__) && !defined(H2D_NO_CLONES)
+#define H2D_CLONES __attribute__((target_clones("default", "arch=x86-64-v3", "arch=x86-64-v4")))
+#else
+#define H2D_CLONES
+#endif
+
+#define H2D_ROW_KERNEL(NAME, ARITH)                                                             \
+  H2D_CLONES void NAME(const float* __restrict__ row, const float* __restrict__ up,            \
+                       const float* __restrict__ dn, float* __restrict__ out, int32_t y0,       \
+                       int32_t y1, const Coef* kp) {                                            \
+    const Coef k = *kp;                                                                         \
+    _Pragma("omp simd")                                                                         \
+    for (int32_t y = y0; y <= y1; ++y)                                                          \
+      out[y] = point<ARITH>(row[y], up[y], dn[y], row[y - 1], row[y + 1], k);                   \
+  }
+H2D_ROW_KERNEL(row_fp32, H2D_ARITH_FP32)
+H2D_ROW_KERNEL(row_strict, H2D_ARITH_STRICT)
+H2D_ROW_KERNEL(row_strict_fma, H2D_ARITH_STRICT_FMA)
+#undef H2D_ROW_KERNEL
+
+typedef void (*row_fn_t)(const float*, const float*, const float*, float*, int32_t, int32_t, const Coef*);
+
 template <int ARITH>
 void sweep_dense(const float* __restrict__ s, float* __restrict__ d, int32_t nx, int32_t ny,
                  const Active& a, const Coef& k, int threads) {
   // Cells outside the active range keep their value.
   (void)threads;
-#pragma omp parallel for schedule(static) num_threads(threads) if (threads > 1)
+  const row_fn_t fn = ARITH == H2D_ARITH_FP32 ? row_fp32 : ARITH == H2D_ARITH_STRICT ? row_strict : row_strict_fma;
+  const std::vector<float> zeros((size_t)ny, 0.0f);   // the row above row 0 / below row nx-1
+  const float* zrow = zeros.data();
+  // dynamic: on a shared box one preempted thread must not hold up a whole static sweep
+#pragma omp parallel for schedule(dynamic, 16) num_threads(threads) if (threads > 1)
   for (int32_t x = 0; x < nx; ++x) {
     const float* row = s + (int64_t)x * ny;
     float* out = d + (int64_t)x * ny;
-    if (x < a.x_lo || x > a.x_hi) {
+    if (x < a.x_lo || x > a.x_hi || a.y_lo > a.y_hi) {
       std::memcpy(out, row, sizeof(float) * (size_t)ny);
       continue;
     }
-    const float* up = (x > 0) ? row - ny : nullptr;
-    const float* dn = (x < nx - 1) ? row + ny : nullptr;
-    for (int32_t y = 0; y < ny; ++y) {
-      if (y < a.y_lo || y > a.y_hi) {
-        out[y] = row[y];
-        continue;
-      }
-      float xm = up ? up[y] : 0.0f;
-      float xp = dn ? dn[y] : 0.0f;
-      float ym = (y > 0) ? row[y - 1] : 0.0f;
-      float yp = (y < ny - 1) ? row[y + 1] : 0.0f;
-      out[y] = point<ARITH>(row[y], xm, xp, ym, yp, k);
-    }
+    const float* up = (x > 0) ? row - ny : zrow;
+    const float* dn = (x < nx - 1) ? row + ny : zrow;
+    // inactive columns at both ends copy through
+    for (int32_t y = 0; y < a.y_lo; ++y) out[y] = row[y];
+    for (int32_t y = a.y_hi + 1; y < ny; ++y) out[y] = row[y];
+    // active columns that have both horizontal neighbours inside the grid
+    const int32_t y0 = a.y_lo > 1 ? a.y_lo : 1;
+    const int32_t y1 = a.y_hi < ny - 2 ? a.y_hi : ny - 2;
+    if (y0 <= y1) fn(row, up, dn, out, y0, y1, &k);
+    // active grid-edge columns (ghost-ring mode): the missing neighbour reads 0
+    if (a.y_lo == 0) out[0] = point<ARITH>(row[0], up[0], dn[0], 0.0f, ny > 1 ? row[1] : 0.0f, k);
+    if (a.y_hi == ny - 1 && ny > 1)
+      out[ny - 1] = point<ARITH>(row[ny - 1], up[ny - 1], dn[ny - 1], row[ny - 2], 0.0f, k);
   }
 }
 
