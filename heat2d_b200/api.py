@@ -10,18 +10,20 @@ from __future__ import annotations
 
 from typing import Optional, Tuple
 
-import torch
-import torch.distributed as dist
+from ._lazy import LazyModule
+
+torch = LazyModule("torch")
+dist = LazyModule("torch.distributed")
 
 from .config import HeatConfig
 
 
 def make_solver(cfg: HeatConfig, device=None):
     """Pick the solver class for `cfg.backend` and the current process group."""
-    world = dist.get_world_size() if dist.is_initialized() else 1
-    if cfg.backend == "cpu":
+    if cfg.backend == "cpu":   # needs neither torch nor a process group
         from .models.cpu import CpuSolver
         return CpuSolver(cfg)
+    world = dist.get_world_size() if dist.is_initialized() else 1
     if cfg.backend == "nccl-halo":
         from .parallel.dist import HaloExchangeSolver
         return HaloExchangeSolver(cfg, device)

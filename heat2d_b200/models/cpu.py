@@ -54,6 +54,10 @@ class CpuSolver:
         self.steps_done += done
         return CpuResult(self.steps_done, self.steps_done, conv, last, el, cfg.nx, cfg.ny, done)
 
-    def gather(self):
+    def gather(self, as_numpy: bool = False):
+        """The current field on the host: a torch tensor sharing the memory (like the GPU
+        solvers' `gather`), or the numpy array itself with ``as_numpy=True`` (no torch import)."""
+        if as_numpy:
+            return self.u
         import torch
         return torch.from_numpy(self.u)

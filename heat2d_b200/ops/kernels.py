@@ -9,9 +9,11 @@ import ctypes as C
 from typing import Optional
 
 import numpy as np
-import torch
 
 from .. import _native as N
+from .._lazy import LazyModule
+
+torch = LazyModule("torch")   # only the CUDA wrappers need it; the CPU oracle does not
 
 # ------------------------------------------------------------------- helpers
 

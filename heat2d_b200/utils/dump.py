@@ -17,12 +17,12 @@ from .. import _native as N
 
 
 def _as_host(u) -> np.ndarray:
-    try:
-        import torch
-        if isinstance(u, torch.Tensor):
-            u = u.detach().cpu().numpy()
-    except ImportError:  # pragma: no cover
-        pass
+    # a torch tensor can only show up if torch is already imported: do not import it here
+    # (the CPU backend runs without it)
+    import sys
+    torch = sys.modules.get("torch")
+    if torch is not None and isinstance(u, torch.Tensor):
+        u = u.detach().cpu().numpy()
     return np.ascontiguousarray(u, dtype=np.float32)
 
 

@@ -112,3 +112,19 @@ def test_given_program_worker_limits():
     assert config_from_args(a).px == 2
     r = run_cli("--preset", "mpi_heat2Dn", "--px", "2", "--backend", "fused")
     assert r.returncode == 1 and "between 4 and 9" in r.stderr
+
+
+def test_cpu_backend_runs_without_importing_torch(tmp_path):
+    """`--backend cpu` needs neither PyTorch nor a GPU; importing torch would be most of the
+    run time of a reference-size job."""
+    import subprocess
+    import sys
+    code = ("import sys; from heat2d_b200 import cli; "
+            f"rc = cli.main(['--preset', 'grad1612_hybrid', '--backend', 'cpu', '--debug', '--out-dir', r'{tmp_path}']); "
+            "print('TORCH', 'torch' in sys.modules, rc)")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120,
+                       env=dict(os.environ, PYTHONPATH=root))
+    assert r.returncode == 0, r.stderr
+    assert "TORCH False 0" in r.stdout
+    assert (tmp_path / "final.dat").exists() and (tmp_path / "final_binary.dat").exists()
