@@ -252,29 +252,49 @@ int h2d_cpu_step_tile(const float* src, float* dst, const h2d_tile_t* t, const h
     return h2d_fail(H2D_EINVAL, "h2d_cpu_step_tile: needs a margin of at least 1");
   const Coef k = make_coef(phys);
   const Active a = active_range(t->nx, t->ny, phys->boundary);
+  const row_fn_t fn = phys->arith == H2D_ARITH_FP32     ? row_fp32
+                      : phys->arith == H2D_ARITH_STRICT ? row_strict
+                                                        : row_strict_fma;
+  // Rows above / below the GRID read as zeros whatever the margin holds; they are indexed
+  // with tile-local columns -1 .. cols, hence the offset of one.
+  const std::vector<float> zeros((size_t)t->cols + 2, 0.0f);
+  const float* zrow = zeros.data() + 1;
+  // tile-local range of active columns
+  const int32_t j_lo = a.y_lo - t->y0 > 0 ? a.y_lo - t->y0 : 0;
+  const int32_t j_hi = a.y_hi - t->y0 < t->cols - 1 ? a.y_hi - t->y0 : t->cols - 1;
   for (int32_t i = 0; i < t->rows; ++i) {
     const float* row = src + (int64_t)(i + t->halo_r) * t->pitch + t->halo_c;
     float* out = dst + (int64_t)(i + t->halo_r) * t->pitch + t->halo_c;
     const int32_t gx = t->x0 + i;
-    for (int32_t j = 0; j < t->cols; ++j) {
-      const int32_t gy = t->y0 + j;
-      const bool act = gx >= a.x_lo && gx <= a.x_hi && gy >= a.y_lo && gy <= a.y_hi;
-      if (!act) {
-        out[j] = row[j];
-        continue;
-      }
-      // Reads outside the global grid see 0 (ghost-ring mode only gets here).
-      float xm = (gx > 0) ? row[j - t->pitch] : 0.0f;
-      float xp = (gx < t->nx - 1) ? row[j + t->pitch] : 0.0f;
-      float ym = (gy > 0) ? row[j - 1] : 0.0f;
-      float yp = (gy < t->ny - 1) ? row[j + 1] : 0.0f;
-      float c = row[j];
-      switch (phys->arith) {
-        case H2D_ARITH_FP32: out[j] = point<H2D_ARITH_FP32>(c, xm, xp, ym, yp, k); break;
-        case H2D_ARITH_STRICT: out[j] = point<H2D_ARITH_STRICT>(c, xm, xp, ym, yp, k); break;
-        default: out[j] = point<H2D_ARITH_STRICT_FMA>(c, xm, xp, ym, yp, k); break;
-      }
+    if (gx < a.x_lo || gx > a.x_hi || j_lo > j_hi) {
+      std::memcpy(out, row, sizeof(float) * (size_t)t->cols);
+      continue;
     }
+    const float* up = (gx > 0) ? row - t->pitch : zrow;
+    const float* dn = (gx < t->nx - 1) ? row + t->pitch : zrow;
+    for (int32_t j = 0; j < j_lo; ++j) out[j] = row[j];
+    for (int32_t j = j_hi + 1; j < t->cols; ++j) out[j] = row[j];
+    // Columns whose horizontal neighbours are inside the grid: the margin supplies them
+    // at tile edges.  Grid-edge columns (ghost-ring mode) read a zero instead.
+    int32_t j0 = j_lo, j1 = j_hi;
+    if (t->y0 + j0 == 0) {
+      const float yp = t->ny > 1 ? row[j0 + 1] : 0.0f;
+      switch (phys->arith) {
+        case H2D_ARITH_FP32: out[j0] = point<H2D_ARITH_FP32>(row[j0], up[j0], dn[j0], 0.0f, yp, k); break;
+        case H2D_ARITH_STRICT: out[j0] = point<H2D_ARITH_STRICT>(row[j0], up[j0], dn[j0], 0.0f, yp, k); break;
+        default: out[j0] = point<H2D_ARITH_STRICT_FMA>(row[j0], up[j0], dn[j0], 0.0f, yp, k); break;
+      }
+      ++j0;
+    }
+    if (j1 >= j0 && t->y0 + j1 == t->ny - 1) {
+      switch (phys->arith) {
+        case H2D_ARITH_FP32: out[j1] = point<H2D_ARITH_FP32>(row[j1], up[j1], dn[j1], row[j1 - 1], 0.0f, k); break;
+        case H2D_ARITH_STRICT: out[j1] = point<H2D_ARITH_STRICT>(row[j1], up[j1], dn[j1], row[j1 - 1], 0.0f, k); break;
+        default: out[j1] = point<H2D_ARITH_STRICT_FMA>(row[j1], up[j1], dn[j1], row[j1 - 1], 0.0f, k); break;
+      }
+      --j1;
+    }
+    if (j0 <= j1) fn(row, up, dn, out, j0, j1, &k);
   }
   return H2D_OK;
 }

@@ -136,6 +136,11 @@ int h2d_dump_rowmajor(const char* path, const float* u, int32_t nx, int32_t ny);
  * sets the file length to nx*ny*4 first (the reference never truncates).      */
 int h2d_dump_binary_tile(const char* path, const float* owned, int64_t owned_pitch,
                          const h2d_tile_t* tile, int truncate);
+/* Test hooks for the text writers' own "%6.1f" formatter: format one value into out64
+ * (at least 64 bytes; returns the length), and compare it with snprintf over `count` float
+ * bit patterns first, first + stride, ... (returns the number of mismatches).           */
+int h2d_format_6_1f(float v, char* out64);
+int64_t h2d_format_6_1f_check(uint32_t first, uint64_t count, uint32_t stride, uint32_t* first_bad);
 /* rank 0: convert the binary file to text (grad1612_mpi_heat.c:191-203). */
 int h2d_binary_to_text(const char* bin_path, const char* txt_path, int32_t nx, int32_t ny,
                        int format /*0 = rowmajor, 1 = prtdat*/);

@@ -78,3 +78,24 @@ def test_dump_dispatch(tmp_path):
     assert D.dump("none", str(tmp_path), "initial", u) is None
     assert D.dump("prtdat", str(tmp_path), "initial", u).endswith("initial.dat")
     assert D.dump("binary", str(tmp_path), "final", u).endswith("final_binary.dat")
+
+
+def test_own_6_1f_formatter_equals_printf():
+    """The text writers format "%6.1f" themselves (csrc/dump.cpp::fmt61); every sampled float
+    bit pattern — ties, negative zero, subnormals, huge values, inf, nan — must give printf's bytes.
+    (All 2^32 patterns were compared once when the formatter was written: no mismatch.)"""
+    import ctypes as C
+    from heat2d_b200 import _native as N
+    lib = N.cpu()
+    lib.h2d_format_6_1f_check.argtypes = [C.c_uint32, C.c_uint64, C.c_uint32, C.POINTER(C.c_uint32)]
+    lib.h2d_format_6_1f_check.restype = C.c_int64
+    lib.h2d_format_6_1f.argtypes = [C.c_float, C.c_char_p]
+    bad = C.c_uint32(0)
+    # 4 Mi patterns spread over the whole 32-bit space, plus a dense run around 1.0 and around -0.05
+    assert lib.h2d_format_6_1f_check(0, 1 << 22, 1021, C.byref(bad)) == 0, hex(bad.value)
+    assert lib.h2d_format_6_1f_check(0x3F7FF000, 1 << 16, 1, C.byref(bad)) == 0, hex(bad.value)
+    assert lib.h2d_format_6_1f_check(0xBD4CC000, 1 << 16, 1, C.byref(bad)) == 0, hex(bad.value)
+    buf = C.create_string_buffer(64)
+    for v in (0.0, -0.0, 0.05, 0.25, 0.75, -0.04, 9.95, 99999.95, 1e18, 3e38, float("inf"), float("nan")):
+        n = lib.h2d_format_6_1f(v, buf)
+        assert buf.raw[:n].decode() == "%6.1f" % C.c_float(v).value
