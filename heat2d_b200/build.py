@@ -44,10 +44,12 @@ def _nvcc() -> str:
 
 
 def _newer(target: Path, deps) -> bool:
+    """True if `target` exists and no source is newer.  An installed copy of the package has
+    the libraries but not the sources (csrc/, include/): the libraries are then used as is."""
     if not target.exists():
         return False
     t = target.stat().st_mtime
-    return all(Path(d).stat().st_mtime <= t for d in deps)
+    return all(not Path(d).exists() or Path(d).stat().st_mtime <= t for d in deps)
 
 
 def _headers():
