@@ -808,6 +808,17 @@ static int choose_chunk_rows(int rows, int cols, int kmax, int min_waves = 1) {
   return best_R;
 }
 
+// Waves of tasks a launch of a plan WITH neighbours keeps at least (see choose_chunk_rows).
+// Tuning hook for sweeps on several GPUs without rebuilding: H2D_MIN_WAVES=1..16.
+static int peer_min_waves() {
+  const char* e = getenv("H2D_MIN_WAVES");
+  if (e && e[0]) {
+    const int v = atoi(e);
+    if (v >= 1 && v <= 16) return v;
+  }
+  return 4;
+}
+
 static void plan_counts(const h2d_tile_t* t, int kmax, int chunk_rows, int* n_chunks,
                         int* max_tasks, int min_waves = 1) {
   int R = chunk_rows > 0 ? chunk_rows : choose_chunk_rows(t->rows, t->cols, kmax, min_waves);
@@ -889,14 +900,14 @@ extern "C" {
 
 int32_t h2d_plan_chunk_rows(const h2d_tile_t* tile, int32_t kmax, int32_t with_peers) {
   if (!tile || kmax < 1 || kmax > TK_KMAX || tile->rows < 1 || tile->cols < 1) return 0;
-  return choose_chunk_rows(tile->rows, tile->cols, kmax, with_peers ? 4 : 1);
+  return choose_chunk_rows(tile->rows, tile->cols, kmax, with_peers ? peer_min_waves() : 1);
 }
 
 size_t h2d_plan_scratch_bytes(const h2d_tile_t* tile, int32_t kmax, int32_t chunk_rows) {
   if (!tile || kmax < 1 || kmax > TK_KMAX || tile->rows < 1 || tile->cols < 1) return 0;
   int nc, mt, nc2, mt2;
   plan_counts(tile, kmax, chunk_rows, &nc, &mt);
-  plan_counts(tile, kmax, chunk_rows, &nc2, &mt2, 4);   // plans with peers use more, shorter chunks
+  plan_counts(tile, kmax, chunk_rows, &nc2, &mt2, peer_min_waves());   // plans with peers use more, shorter chunks
   if (mt2 > mt) mt = mt2;
   return scratch_layout_bytes(mt);
 }
@@ -962,7 +973,7 @@ h2d_plan_t* h2d_plan_create(const h2d_plan_desc_t* d) {
   p->has_peers = has_peers;
   cudaGetDevice(&p->device);
   int max_tasks = 0;
-  const int min_waves = has_peers ? 4 : 1;
+  const int min_waves = has_peers ? peer_min_waves() : 1;
   plan_counts(&t, d->kmax, d->chunk_rows, &p->n_chunks, &max_tasks, min_waves);
   p->chunk_rows = d->chunk_rows > 0 ? d->chunk_rows : choose_chunk_rows(t.rows, t.cols, d->kmax, min_waves);
   if (p->n_chunks == 1) p->chunk_rows = t.rows;
