@@ -59,7 +59,10 @@ def _headers():
 def _run(cmd, verbose, log_path=None):
     res = subprocess.run(cmd, capture_output=True, text=True)
     if log_path is not None:
-        Path(log_path).write_text(res.stdout + res.stderr)
+        # the ptxas -v logs are kept in the repository (register / spill evidence): drop the
+        # one line that changes from build to build
+        text = "\n".join(l for l in (res.stdout + res.stderr).splitlines() if "Compile time" not in l)
+        Path(log_path).write_text(text + "\n")
     if res.returncode != 0:
         raise RuntimeError("build failed: %s\n%s\n%s" % (" ".join(map(str, cmd)), res.stdout, res.stderr))
     if verbose:
