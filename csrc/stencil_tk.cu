@@ -437,7 +437,23 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    const int2 tk = a.tasks != nullptr ? a.tasks[task] : make_int2(task % a.n_strips, task / a.n_strips);
+    int2 tk;
+    if (a.tasks != nullptr) {
+      tk = a.tasks[task];
+    } else if (XTR && a.has_peers) {
+      // Row window of a tile with W / E neighbours (pipelined solve): no task list; the
+      // tasks of the first and the last strip — the ones that hold the 32-column bands —
+      // come first, chunk by chunk, then the interior strips.
+      const int ns = a.n_strips, ne = ns >= 2 ? 2 : 1, n_edge = ne * a.n_chunks;
+      if (task < n_edge) {
+        tk = make_int2((int)(((unsigned)((task % ne) ? ns - 1 : 0)) | 0x80000000u), task / ne);
+      } else {
+        const int t2 = task - n_edge;
+        tk = make_int2(1 + t2 % (ns - ne), t2 / (ns - ne));
+      }
+    } else {
+      tk = make_int2(task % a.n_strips, task / a.n_strips);
+    }
     const int strip = tk.x & 0x7fffffff;
     const bool comm_edge = XTR && (tk.x < 0) && a.has_peers;
     const int chunk = tk.y;
@@ -1017,6 +1033,18 @@ h2d_plan_t* h2d_plan_create(const h2d_plan_desc_t* d) {
   return p;
 }
 
+// H2D_DEBUG_NOFWD=1: skip the peer stores (timing experiments); H2D_DEBUG_DELAY=1: random
+// per-task delays around the flag protocol (stress test).
+static int debug_flags() {
+  static int dbg = -1;
+  if (dbg < 0) {
+    const char* e = getenv("H2D_DEBUG_NOFWD");
+    const char* d = getenv("H2D_DEBUG_DELAY");
+    dbg = ((e && e[0] == '1') ? 1 : 0) | ((d && d[0] == '1') ? 2 : 0);
+  }
+  return dbg;
+}
+
 int h2d_plan_launch(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int norm, void* stream) {
   return h2d_plan_launch_ex(p, src_parity, k, epoch, norm, nullptr, 0u, stream);
 }
@@ -1076,15 +1104,7 @@ int h2d_plan_launch_ex(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int
   a.timeout_ns = p->desc.spin_timeout_ns > 0 ? p->desc.spin_timeout_ns : 10000000000LL;
   a.ctl = ctl;
   a.run_if = run_if;
-  {
-    static int dbg = -1;
-    if (dbg < 0) {
-      const char* e = getenv("H2D_DEBUG_NOFWD");
-      const char* d = getenv("H2D_DEBUG_DELAY");
-      dbg = ((e && e[0] == '1') ? 1 : 0) | ((d && d[0] == '1') ? 2 : 0);
-    }
-    a.debug = dbg;
-  }
+  a.debug = debug_flags();
 
   const int grid = (tl.n_tasks + TK_WARPS - 1) / TK_WARPS;
   fn<<<grid, TK_WARPS * 32, TK_SMEM_BYTES, (cudaStream_t)stream>>>(p->tmap[src_parity], a);
@@ -1111,9 +1131,10 @@ int h2d_plan_run_many(h2d_plan_t* const* plans, int n_plans, int src_parity, int
 // (no peers, no norm): tasks are enumerated arithmetically, chunk c starts at
 // row_base + c * R.
 static int launch_window(h2d_plan* p, int src_parity, int k, int row_base, int row_end, int chunk_rows,
-                         cudaStream_t st) {
+                         cudaStream_t st, uint32_t epoch = 0u) {
   if (row_end <= row_base) return H2D_OK;
-  tk_fn_t fn = tk_pick(k, p->desc.phys.arith, coef_is_reference(p->geo, p->desc.phys.arith), false);
+  const bool peers = p->has_peers;
+  tk_fn_t fn = tk_pick(k, p->desc.phys.arith, coef_is_reference(p->geo, p->desc.phys.arith), peers);
   if (!fn) return h2d_fail(H2D_EINVAL, "launch_window: no kernel for k = %d", k);
   const int H = round_up4(k);
   TkArgs a;
@@ -1137,7 +1158,24 @@ static int launch_window(h2d_plan* p, int src_parity, int k, int row_base, int r
   a.fault = hdr + 3;
   a.stats = (unsigned long long*)(hdr + 8);
   a.cta_partials = (float*)((char*)p->scratch + 256);
-  a.timeout_ns = 10000000000LL;
+  a.timeout_ns = p->desc.spin_timeout_ns > 0 ? p->desc.spin_timeout_ns : 10000000000LL;
+  if (peers) {
+    // W / E neighbours only (checked by the caller): the first and last strip of every
+    // chunk forward the column bands and take part in the epoch protocol.
+    a.has_peers = 1;
+    a.n_comm_edge = (a.n_strips >= 2 ? 2 : 1) * a.n_chunks;
+    for (int d = 0; d < H2D_NDIR; ++d) {
+      const h2d_peer_t& pr = p->desc.peer[d];
+      a.peer[d].buf = pr.buf[1 - src_parity];
+      a.peer[d].flag = pr.flag;
+      a.peer[d].x0 = pr.x0; a.peer[d].y0 = pr.y0;
+      a.peer[d].halo_r = pr.halo_r; a.peer[d].halo_c = pr.halo_c;
+      a.peer[d].pitch = pr.pitch;
+    }
+    a.flags_in = p->desc.flags_in;
+    a.epoch = epoch;
+    a.debug = debug_flags();
+  }
   const int grid = (a.n_tasks + TK_WARPS - 1) / TK_WARPS;
   fn<<<grid, TK_WARPS * 32, TK_SMEM_BYTES, st>>>(p->tmap[src_parity], a);
   H2D_CHECK_LAUNCH("tk_kernel (row window)");
@@ -1224,32 +1262,74 @@ int h2d_plan_run_dataflow(h2d_plan_t* p, int src_parity, int k, int n_epochs, vo
   return H2D_OK;
 }
 
+// Rows of one wave of window tasks for this plan (see h2d_plan_solve_pipelined): ranks of a
+// column-strip run agree on the minimum of this value so that they cut the same blocks.
+static int pipelined_chunk_rows(const h2d_plan* p) {
+  int R = p->chunk_rows;
+  while (R > 384) R = (R + 1) / 2;
+  return R;
+}
+static int pipelined_wave_rows(const h2d_plan* p) {
+  const int wv_ = TK_W - 2 * round_up4(p->desc.kmax);
+  const int ns_ = (p->desc.tile.cols + wv_ - 1) / wv_;
+  const double slots_ = (double)sm_count() * (p->desc.kmax <= 5 ? 16 : 12);
+  int m1 = (int)(slots_ / ns_);
+  if (m1 < 1) m1 = 1;
+  return m1 * pipelined_chunk_rows(p);
+}
+
+int32_t h2d_plan_wave_rows(const h2d_plan_t* p) { return p ? pipelined_wave_rows(p) : 0; }
+
 int h2d_plan_solve_pipelined(h2d_plan_t* p, const float* host_in, int64_t in_pitch, float* host_out,
                              int64_t out_pitch, int64_t steps, int k, int block_rows, int skew_rows,
                              void* stream, int* final_parity) {
+  if (p && p->has_peers) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: single-tile plans only (see _ex)");
+  return h2d_plan_solve_pipelined_ex(p, host_in, in_pitch, host_out, out_pitch, steps, k, block_rows, skew_rows,
+                                     0, 0u, stream, final_parity, nullptr);
+}
+
+int h2d_plan_solve_pipelined_ex(h2d_plan_t* p, const float* host_in, int64_t in_pitch, float* host_out,
+                                int64_t out_pitch, int64_t steps, int k, int block_rows, int skew_rows,
+                                int wave_rows, uint32_t epoch0, void* stream, int* final_parity,
+                                uint32_t* epochs_used) {
   if (!p || !host_in || !host_out || steps < 0)
     return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: bad argument");
-  if (p->has_peers) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: single-tile plans only");
   if (k < 1 || k > p->desc.kmax) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: k = %d outside [1, %d]", k, p->desc.kmax);
   const h2d_tile_t& t = p->desc.tile;
   if (in_pitch < t.cols || out_pitch < t.cols) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: host pitch < cols");
+  // Neighbours: column strips only.  Every rank then owns ALL rows, cuts the same row
+  // blocks and issues the same sequence of window launches, one epoch each; the W / E
+  // bands travel per window exactly as they do per launch.  (Row strips cannot be
+  // pipelined this way: a strip's top halo is produced by the LAST block of the strip
+  // above it.)  The level-0 ghost columns come from the host: host_in must hold
+  // TK_WE_COLS valid columns to the left / right of the owned ones where a W / E
+  // neighbour exists.
+  const bool has_w = p->desc.peer[H2D_W].buf[0] != nullptr, has_e = p->desc.peer[H2D_E].buf[0] != nullptr;
+  if (p->has_peers) {
+    for (int d = 0; d < H2D_NDIR; ++d)
+      if (d != H2D_W && d != H2D_E && p->desc.peer[d].buf[0] != nullptr)
+        return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: neighbours other than W / E (use a 1 x P process grid)");
+    if ((t.cols & 3) != 0 || t.cols < 2 * TK_WE_COLS || t.halo_c < TK_WE_COLS ||
+        (has_w && p->desc.peer[H2D_W].halo_c < TK_WE_COLS) || (has_e && p->desc.peer[H2D_E].halo_c < TK_WE_COLS))
+      return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: column strips need cols %% 4 == 0, cols >= %d and %d-column margins",
+                      2 * TK_WE_COLS, TK_WE_COLS);
+    if (in_pitch < t.cols + (has_w ? TK_WE_COLS : 0) + (has_e ? TK_WE_COLS : 0))
+      return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: host_in pitch leaves no room for the ghost columns");
+  }
+  const int up_c0 = has_w ? -TK_WE_COLS : 0;                                  // first uploaded column (tile-local)
+  const int up_w = t.cols + (has_w ? TK_WE_COLS : 0) + (has_e ? TK_WE_COLS : 0);
+  uint32_t epoch = epoch0;
   const int rows = t.rows;
   // windows are a few waves of tasks only: shorter chunks than whole-grid launches use
   // (measured on B200, 32768^2: chunks of ~320 rows and blocks of ~7600 rows are best)
-  int R = p->chunk_rows;
-  while (R > 384) R = (R + 1) / 2;
+  const int R = pipelined_chunk_rows(p);
   const int S = skew_rows > 0 ? skew_rows : k + 4;       // rows the processed window moves up per launch
   if (S < k + 1) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: skew %d must exceed k = %d", S, k);
   const int L = (int)((steps + k - 1) / k);              // launches ("levels") per block
   // Block sizes.  Large blocks compute efficiently (several waves of tasks per launch) but
   // the first block delays the start by its upload and the last one exposes its download, so
   // the sizes ramp up from one wave of tasks to `block_rows` (0 = four waves) and down again.
-  const int wv_ = TK_W - 2 * round_up4(p->desc.kmax);
-  const int ns_ = (t.cols + wv_ - 1) / wv_;
-  const double slots_ = (double)sm_count() * (p->desc.kmax <= 5 ? 16 : 12);
-  int m1 = (int)(slots_ / ns_);                           // chunks per launch for one wave
-  if (m1 < 1) m1 = 1;
-  const int M1 = m1 * R;
+  const int M1 = wave_rows > 0 ? wave_rows : pipelined_wave_rows(p);   // rows of one wave of tasks
   int M = block_rows > 0 ? block_rows : 4 * M1;
   if (M < S + 1) M = S + 1;
   cudaStream_t cs = (cudaStream_t)stream;
@@ -1282,9 +1362,9 @@ int h2d_plan_solve_pipelined(h2d_plan_t* p, const float* host_in, int64_t in_pit
   std::vector<cudaEvent_t> up(n_units);
   for (int u = 0; u < n_units; ++u) {
     const int r0 = u * U, r1 = r0 + U < rows ? r0 + U : rows;
-    H2D_CUDA_TRY(cudaMemcpy2DAsync(dev_row(0, r0), (size_t)t.pitch * 4, host_in + (int64_t)r0 * in_pitch,
-                                   (size_t)in_pitch * 4, (size_t)t.cols * 4, (size_t)(r1 - r0),
-                                   cudaMemcpyHostToDevice, p->s_h2d));
+    H2D_CUDA_TRY(cudaMemcpy2DAsync(dev_row(0, r0) + up_c0, (size_t)t.pitch * 4,
+                                   host_in + (int64_t)r0 * in_pitch + up_c0, (size_t)in_pitch * 4,
+                                   (size_t)up_w * 4, (size_t)(r1 - r0), cudaMemcpyHostToDevice, p->s_h2d));
     if (int rc = new_event(&up[u])) return rc;
     H2D_CUDA_TRY(cudaEventRecord(up[u], p->s_h2d));
   }
@@ -1332,7 +1412,8 @@ int h2d_plan_solve_pipelined(h2d_plan_t* p, const float* host_in, int64_t in_pit
       if (lo < 0) lo = 0;
       if (hi > rows) hi = rows;
       const int kk = (e < L - 1) ? k : (int)(steps - (int64_t)(L - 1) * k);
-      if (int rc = launch_window(p, e & 1, kk, (int)lo, (int)hi, R, cs)) return rc;
+      if (int rc = launch_window(p, e & 1, kk, (int)lo, (int)hi, R, cs, epoch)) return rc;
+      ++epoch;   // one epoch per issued window, on every rank alike
     }
     // rows below b_hi - S*(L-1) now hold the final field
     int64_t fin = b_hi - (int64_t)S * (L - 1);
@@ -1363,6 +1444,7 @@ int h2d_plan_solve_pipelined(h2d_plan_t* p, const float* host_in, int64_t in_pit
   H2D_CUDA_TRY(cudaEventRecord(e_end2, p->s_h2d));
   H2D_CUDA_TRY(cudaStreamWaitEvent(cs, e_end2, 0));
   if (final_parity) *final_parity = out_par;
+  if (epochs_used) *epochs_used = epoch - epoch0;
   return H2D_OK;
 }
 
