@@ -1331,6 +1331,10 @@ int h2d_plan_solve_pipelined_ex(h2d_plan_t* p, const float* host_in, int64_t in_
   // the sizes ramp up from one wave of tasks to `block_rows` (0 = four waves) and down again.
   const int M1 = wave_rows > 0 ? wave_rows : pipelined_wave_rows(p);   // rows of one wave of tasks
   int M = block_rows > 0 ? block_rows : 4 * M1;
+  // Narrow tiles (column strips on many GPUs: 37 task strips at 4096 columns) reach one wave
+  // of tasks only with thousands of rows; keep at least ~4 blocks so that upload, compute and
+  // download still overlap, but never less than one full wave per window.
+  if (block_rows <= 0 && M > rows / 4) M = M1 > rows / 4 ? M1 : rows / 4;
   if (M < S + 1) M = S + 1;
   cudaStream_t cs = (cudaStream_t)stream;
   if (!p->s_h2d) H2D_CUDA_TRY(cudaStreamCreateWithFlags(&p->s_h2d, cudaStreamNonBlocking));
