@@ -126,6 +126,10 @@ def cuda():
                                                         C.c_int, C.c_int, C.c_uint32, vp, P(C.c_int),
                                                         P(C.c_uint32)]
             lib.h2d_plan_solve_pipelined_ex.restype = C.c_int
+            lib.h2d_plan_solve_pipelined_many.argtypes = [P(vp), C.c_int, P(vp), P(C.c_int64), P(vp), P(C.c_int64),
+                                                          C.c_int64, C.c_int, C.c_int, C.c_int, C.c_uint32, vp,
+                                                          P(C.c_int), P(C.c_uint32)]
+            lib.h2d_plan_solve_pipelined_many.restype = C.c_int
             lib.h2d_plan_wave_rows.argtypes = [vp]
             lib.h2d_plan_wave_rows.restype = C.c_int32
             lib.h2d_plan_run_dataflow.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]

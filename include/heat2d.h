@@ -267,6 +267,13 @@ int h2d_plan_solve_pipelined_ex(h2d_plan_t* plan, const float* host_in, int64_t 
                                 int64_t out_pitch, int64_t steps, int k, int block_rows, int skew_rows,
                                 int wave_rows, uint32_t epoch0, void* stream, int* final_parity,
                                 uint32_t* epochs_used);
+/* The tiles of a 1 x P grid emulated in ONE process (several plans, one compute stream):
+ * every window launch is issued for every plan before the next one.  Arrays have one entry
+ * per plan; the block granularity is the minimum over the plans.                          */
+int h2d_plan_solve_pipelined_many(h2d_plan_t* const* plans, int n_plans, const float* const* host_in,
+                                  const int64_t* in_pitch, float* const* host_out, const int64_t* out_pitch,
+                                  int64_t steps, int k, int block_rows, int skew_rows, uint32_t epoch0,
+                                  void* stream, int* final_parity, uint32_t* epochs_used);
 /* Rows that one wave of window tasks covers for this plan (block granularity above). */
 int32_t h2d_plan_wave_rows(const h2d_plan_t* plan);
 
