@@ -188,6 +188,26 @@ def main():
             ev1.synchronize()
             host_in = host_in2
             e2e_how = "Heat2DSolver.solve_pipelined: upload, steps and download overlapped block by block"
+        elif os.environ.get("H2D_BENCH_E2E", "legacy") == "pipelined" and a.impl == "ours" and not a.conv \
+                and not a.weak and ny % (4 * world) == 0 and ny // world >= 64:
+            # several GPUs (opt-in, H2D_BENCH_E2E=pipelined: validated on one GPU with virtual tiles only):
+            # column strips, every rank pipelines upload / windows / download in lockstep
+            scfg = cfg.replace(px=1, py=world)
+            strip = DistributedHeat2DSolver(scfg, device).initialize()
+            hin, col0, host_out = strip.host_strip()
+            sf = strip.fields[0]
+            st = sf.tile
+            hin.copy_(sf.buf[0][st.halo_r:st.halo_r + st.rows, st.halo_c - col0:st.halo_c - col0 + hin.shape[1]])
+            strip.barrier()
+            t0 = time.perf_counter()
+            ev0.record()
+            strip.solve_pipelined(hin, col0, host_out, a.steps)
+            ev1.record()
+            ev1.synchronize()
+            host_in = hin
+            e2e_how = ("DistributedHeat2DSolver.solve_pipelined on a 1x%d grid: per rank upload, window launches with "
+                       "W/E halo exchange and download overlapped block by block, ranks in lockstep" % world)
+            strip.close()
         else:
             ev0.record()
             f.buf[solver.parity].copy_(host_in, non_blocking=True)       # H2D of this rank's inputs

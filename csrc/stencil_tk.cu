@@ -437,7 +437,23 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    const int2 tk = a.tasks != nullptr ? a.tasks[task] : make_int2(task % a.n_strips, task / a.n_strips);
+    int2 tk;
+    if (a.tasks != nullptr) {
+      tk = a.tasks[task];
+    } else if (XTR && a.has_peers) {
+      // Row window of a tile with W / E neighbours (pipelined solve): no task list; the
+      // tasks of the first and the last strip — the ones that hold the 32-column bands —
+      // come first, chunk by chunk, then the interior strips.
+      const int ns = a.n_strips, ne = ns >= 2 ? 2 : 1, n_edge = ne * a.n_chunks;
+      if (task < n_edge) {
+        tk = make_int2((int)(((unsigned)((task % ne) ? ns - 1 : 0)) | 0x80000000u), task / ne);
+      } else {
+        const int t2 = task - n_edge;
+        tk = make_int2(1 + t2 % (ns - ne), t2 / (ns - ne));
+      }
+    } else {
+      tk = make_int2(task % a.n_strips, task / a.n_strips);
+    }
     const int strip = tk.x & 0x7fffffff;
     const bool comm_edge = XTR && (tk.x < 0) && a.has_peers;
     const int chunk = tk.y;
@@ -1017,6 +1033,18 @@ h2d_plan_t* h2d_plan_create(const h2d_plan_desc_t* d) {
   return p;
 }
 
+// H2D_DEBUG_NOFWD=1: skip the peer stores (timing experiments); H2D_DEBUG_DELAY=1: random
+// per-task delays around the flag protocol (stress test).
+static int debug_flags() {
+  static int dbg = -1;
+  if (dbg < 0) {
+    const char* e = getenv("H2D_DEBUG_NOFWD");
+    const char* d = getenv("H2D_DEBUG_DELAY");
+    dbg = ((e && e[0] == '1') ? 1 : 0) | ((d && d[0] == '1') ? 2 : 0);
+  }
+  return dbg;
+}
+
 int h2d_plan_launch(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int norm, void* stream) {
   return h2d_plan_launch_ex(p, src_parity, k, epoch, norm, nullptr, 0u, stream);
 }
@@ -1076,15 +1104,7 @@ int h2d_plan_launch_ex(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int
   a.timeout_ns = p->desc.spin_timeout_ns > 0 ? p->desc.spin_timeout_ns : 10000000000LL;
   a.ctl = ctl;
   a.run_if = run_if;
-  {
-    static int dbg = -1;
-    if (dbg < 0) {
-      const char* e = getenv("H2D_DEBUG_NOFWD");
-      const char* d = getenv("H2D_DEBUG_DELAY");
-      dbg = ((e && e[0] == '1') ? 1 : 0) | ((d && d[0] == '1') ? 2 : 0);
-    }
-    a.debug = dbg;
-  }
+  a.debug = debug_flags();
 
   const int grid = (tl.n_tasks + TK_WARPS - 1) / TK_WARPS;
   fn<<<grid, TK_WARPS * 32, TK_SMEM_BYTES, (cudaStream_t)stream>>>(p->tmap[src_parity], a);
@@ -1111,9 +1131,10 @@ int h2d_plan_run_many(h2d_plan_t* const* plans, int n_plans, int src_parity, int
 // (no peers, no norm): tasks are enumerated arithmetically, chunk c starts at
 // row_base + c * R.
 static int launch_window(h2d_plan* p, int src_parity, int k, int row_base, int row_end, int chunk_rows,
-                         cudaStream_t st) {
+                         cudaStream_t st, uint32_t epoch = 0u) {
   if (row_end <= row_base) return H2D_OK;
-  tk_fn_t fn = tk_pick(k, p->desc.phys.arith, coef_is_reference(p->geo, p->desc.phys.arith), false);
+  const bool peers = p->has_peers;
+  tk_fn_t fn = tk_pick(k, p->desc.phys.arith, coef_is_reference(p->geo, p->desc.phys.arith), peers);
   if (!fn) return h2d_fail(H2D_EINVAL, "launch_window: no kernel for k = %d", k);
   const int H = round_up4(k);
   TkArgs a;
@@ -1137,7 +1158,24 @@ static int launch_window(h2d_plan* p, int src_parity, int k, int row_base, int r
   a.fault = hdr + 3;
   a.stats = (unsigned long long*)(hdr + 8);
   a.cta_partials = (float*)((char*)p->scratch + 256);
-  a.timeout_ns = 10000000000LL;
+  a.timeout_ns = p->desc.spin_timeout_ns > 0 ? p->desc.spin_timeout_ns : 10000000000LL;
+  if (peers) {
+    // W / E neighbours only (checked by the caller): the first and last strip of every
+    // chunk forward the column bands and take part in the epoch protocol.
+    a.has_peers = 1;
+    a.n_comm_edge = (a.n_strips >= 2 ? 2 : 1) * a.n_chunks;
+    for (int d = 0; d < H2D_NDIR; ++d) {
+      const h2d_peer_t& pr = p->desc.peer[d];
+      a.peer[d].buf = pr.buf[1 - src_parity];
+      a.peer[d].flag = pr.flag;
+      a.peer[d].x0 = pr.x0; a.peer[d].y0 = pr.y0;
+      a.peer[d].halo_r = pr.halo_r; a.peer[d].halo_c = pr.halo_c;
+      a.peer[d].pitch = pr.pitch;
+    }
+    a.flags_in = p->desc.flags_in;
+    a.epoch = epoch;
+    a.debug = debug_flags();
+  }
   const int grid = (a.n_tasks + TK_WARPS - 1) / TK_WARPS;
   fn<<<grid, TK_WARPS * 32, TK_SMEM_BYTES, st>>>(p->tmap[src_parity], a);
   H2D_CHECK_LAUNCH("tk_kernel (row window)");
@@ -1224,39 +1262,45 @@ int h2d_plan_run_dataflow(h2d_plan_t* p, int src_parity, int k, int n_epochs, vo
   return H2D_OK;
 }
 
+// Rows of one wave of window tasks for this plan (see h2d_plan_solve_pipelined): ranks of a
+// column-strip run agree on the minimum of this value so that they cut the same blocks.
+static int pipelined_chunk_rows(const h2d_plan* p) {
+  int R = p->chunk_rows;
+  while (R > 384) R = (R + 1) / 2;
+  return R;
+}
+static int pipelined_wave_rows(const h2d_plan* p) {
+  const int wv_ = TK_W - 2 * round_up4(p->desc.kmax);
+  const int ns_ = (p->desc.tile.cols + wv_ - 1) / wv_;
+  const double slots_ = (double)sm_count() * (p->desc.kmax <= 5 ? 16 : 12);
+  int m1 = (int)(slots_ / ns_);
+  if (m1 < 1) m1 = 1;
+  return m1 * pipelined_chunk_rows(p);
+}
+
+int32_t h2d_plan_wave_rows(const h2d_plan_t* p) { return p ? pipelined_wave_rows(p) : 0; }
+
 int h2d_plan_solve_pipelined(h2d_plan_t* p, const float* host_in, int64_t in_pitch, float* host_out,
                              int64_t out_pitch, int64_t steps, int k, int block_rows, int skew_rows,
                              void* stream, int* final_parity) {
-  if (!p || !host_in || !host_out || steps < 0)
-    return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: bad argument");
-  if (p->has_peers) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: single-tile plans only");
-  if (k < 1 || k > p->desc.kmax) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: k = %d outside [1, %d]", k, p->desc.kmax);
-  const h2d_tile_t& t = p->desc.tile;
-  if (in_pitch < t.cols || out_pitch < t.cols) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: host pitch < cols");
-  const int rows = t.rows;
-  // windows are a few waves of tasks only: shorter chunks than whole-grid launches use
-  // (measured on B200, 32768^2: chunks of ~320 rows and blocks of ~7600 rows are best)
-  int R = p->chunk_rows;
-  while (R > 384) R = (R + 1) / 2;
-  const int S = skew_rows > 0 ? skew_rows : k + 4;       // rows the processed window moves up per launch
-  if (S < k + 1) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: skew %d must exceed k = %d", S, k);
-  const int L = (int)((steps + k - 1) / k);              // launches ("levels") per block
-  // Block sizes.  Large blocks compute efficiently (several waves of tasks per launch) but
-  // the first block delays the start by its upload and the last one exposes its download, so
-  // the sizes ramp up from one wave of tasks to `block_rows` (0 = four waves) and down again.
-  const int wv_ = TK_W - 2 * round_up4(p->desc.kmax);
-  const int ns_ = (t.cols + wv_ - 1) / wv_;
-  const double slots_ = (double)sm_count() * (p->desc.kmax <= 5 ? 16 : 12);
-  int m1 = (int)(slots_ / ns_);                           // chunks per launch for one wave
-  if (m1 < 1) m1 = 1;
-  const int M1 = m1 * R;
-  int M = block_rows > 0 ? block_rows : 4 * M1;
-  if (M < S + 1) M = S + 1;
-  cudaStream_t cs = (cudaStream_t)stream;
-  if (!p->s_h2d) H2D_CUDA_TRY(cudaStreamCreateWithFlags(&p->s_h2d, cudaStreamNonBlocking));
-  if (!p->s_d2h) H2D_CUDA_TRY(cudaStreamCreateWithFlags(&p->s_d2h, cudaStreamNonBlocking));
+  if (p && p->has_peers) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: single-tile plans only (see _ex)");
+  return h2d_plan_solve_pipelined_ex(p, host_in, in_pitch, host_out, out_pitch, steps, k, block_rows, skew_rows,
+                                     0, 0u, stream, final_parity, nullptr);
+}
+
+// One plan's share of a pipelined solve: validation, geometry, copy streams and events.
+struct PipeRank {
+  h2d_plan* p = nullptr;
+  const float* host_in = nullptr;
+  float* host_out = nullptr;
+  int64_t in_pitch = 0, out_pitch = 0;
+  int up_c0 = 0, up_w = 0, R = 0;
   size_t ev_used = 0;
-  auto new_event = [&](cudaEvent_t* out) -> int {
+  std::vector<cudaEvent_t> up;   // one event per upload unit
+  int waited = -1;               // last upload unit the compute stream waits for
+  int d2h_done_rows = 0;         // rows [0, d2h_done_rows) already queued for download
+
+  int new_event(cudaEvent_t* out) {
     if (ev_used == p->ev_pool.size()) {
       cudaEvent_t e;
       H2D_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -1264,33 +1308,118 @@ int h2d_plan_solve_pipelined(h2d_plan_t* p, const float* host_in, int64_t in_pit
     }
     *out = p->ev_pool[ev_used++];
     return H2D_OK;
-  };
-  auto dev_row = [&](int parity, int r) -> float* {
+  }
+  float* dev_row(int parity, int r) const {
+    const h2d_tile_t& t = p->desc.tile;
     return p->desc.buf[parity] + (int64_t)(r + t.halo_r) * t.pitch + t.halo_c;
-  };
+  }
+};
 
-  // the copy streams start after whatever the caller queued on `stream`
-  cudaEvent_t e_start;
-  if (int rc = new_event(&e_start)) return rc;
-  H2D_CUDA_TRY(cudaEventRecord(e_start, cs));
-  H2D_CUDA_TRY(cudaStreamWaitEvent(p->s_h2d, e_start, 0));
-  H2D_CUDA_TRY(cudaStreamWaitEvent(p->s_d2h, e_start, 0));
+static int pipe_check(PipeRank& q, int k) {
+  h2d_plan* p = q.p;
+  if (!p || !q.host_in || !q.host_out) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: bad argument");
+  if (k < 1 || k > p->desc.kmax) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: k = %d outside [1, %d]", k, p->desc.kmax);
+  const h2d_tile_t& t = p->desc.tile;
+  if (q.in_pitch < t.cols || q.out_pitch < t.cols) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: host pitch < cols");
+  // Neighbours: column strips only.  Every rank then owns ALL rows, cuts the same row
+  // blocks and issues the same sequence of window launches, one epoch each; the W / E
+  // bands travel per window exactly as they do per launch.  (Row strips cannot be
+  // pipelined this way: a strip's top halo is produced by the LAST block of the strip
+  // above it.)  The level-0 ghost columns come from the host: host_in must hold
+  // TK_WE_COLS valid columns to the left / right of the owned ones where a W / E
+  // neighbour exists.
+  const bool has_w = p->desc.peer[H2D_W].buf[0] != nullptr, has_e = p->desc.peer[H2D_E].buf[0] != nullptr;
+  if (p->has_peers) {
+    for (int d = 0; d < H2D_NDIR; ++d)
+      if (d != H2D_W && d != H2D_E && p->desc.peer[d].buf[0] != nullptr)
+        return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: neighbours other than W / E (use a 1 x P process grid)");
+    if ((t.cols & 3) != 0 || t.cols < 2 * TK_WE_COLS || t.halo_c < TK_WE_COLS ||
+        (has_w && p->desc.peer[H2D_W].halo_c < TK_WE_COLS) || (has_e && p->desc.peer[H2D_E].halo_c < TK_WE_COLS))
+      return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: column strips need cols %% 4 == 0, cols >= %d and %d-column margins",
+                      2 * TK_WE_COLS, TK_WE_COLS);
+    if (q.in_pitch < t.cols + (has_w ? TK_WE_COLS : 0) + (has_e ? TK_WE_COLS : 0))
+      return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: host_in pitch leaves no room for the ghost columns");
+  }
+  q.up_c0 = has_w ? -TK_WE_COLS : 0;                                   // first uploaded column (tile-local)
+  q.up_w = t.cols + (has_w ? TK_WE_COLS : 0) + (has_e ? TK_WE_COLS : 0);
+  q.R = pipelined_chunk_rows(p);
+  q.ev_used = 0;
+  q.waited = -1;
+  q.d2h_done_rows = 0;
+  return H2D_OK;
+}
 
-  // upload in units of U rows, one event per unit
+// The pipelined solve for one or several plans that share one compute stream.  Several plans
+// = the tiles of a 1 x P grid emulated in one process: every window is issued for every plan
+// before the next one, so a plan's flags are always published by launches that precede its
+// neighbours' waits in stream order.  With one plan per process (real ranks) the same code
+// runs with n = 1 on every rank.
+static int pipelined_solve(PipeRank* qs, int n, int64_t steps, int k, int block_rows, int skew_rows,
+                           int wave_rows, uint32_t epoch0, cudaStream_t cs, int* final_parity,
+                           uint32_t* epochs_used) {
+  if (steps < 0 || n < 1) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: bad argument");
+  for (int i = 0; i < n; ++i)
+    if (int rc = pipe_check(qs[i], k)) return rc;
+  const int rows = qs[0].p->desc.tile.rows;
+  for (int i = 1; i < n; ++i)
+    if (qs[i].p->desc.tile.rows != rows)
+      return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: all tiles must own the same rows");
+  uint32_t epoch = epoch0;
+  // windows are a few waves of tasks only: shorter chunks than whole-grid launches use
+  // (measured on B200, 32768^2: chunks of ~320 rows and blocks of ~7600 rows are best)
+  const int S = skew_rows > 0 ? skew_rows : k + 4;       // rows the processed window moves up per launch
+  if (S < k + 1) return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined: skew %d must exceed k = %d", S, k);
+  const int L = (int)((steps + k - 1) / k);              // launches ("levels") per block
+  // Block sizes.  Large blocks compute efficiently (several waves of tasks per launch) but
+  // the first block delays the start by its upload and the last one exposes its download, so
+  // the sizes ramp up from one wave of tasks to `block_rows` (0 = four waves) and down again.
+  int M1 = wave_rows;                                     // rows of one wave of tasks
+  if (M1 <= 0) {
+    M1 = pipelined_wave_rows(qs[0].p);
+    for (int i = 1; i < n; ++i) {
+      const int w = pipelined_wave_rows(qs[i].p);
+      if (w < M1) M1 = w;
+    }
+  }
+  int M = block_rows > 0 ? block_rows : 4 * M1;
+  // Narrow tiles (column strips on many GPUs: 37 task strips at 4096 columns) reach one wave
+  // of tasks only with thousands of rows; keep at least ~4 blocks so that upload, compute and
+  // download still overlap, but never less than one full wave per window.
+  if (block_rows <= 0 && qs[0].p->has_peers && M > rows / 4) M = M1 > rows / 4 ? M1 : rows / 4;
+  if (M < S + 1) M = S + 1;
+
+  // upload in units of U rows, one event per unit; the copy streams start after whatever
+  // the caller queued on `stream`
   const int U = M1 < 1024 ? (M1 < rows ? M1 : rows) : 1024;
   const int n_units = (rows + U - 1) / U;
-  std::vector<cudaEvent_t> up(n_units);
+  for (int i = 0; i < n; ++i) {
+    PipeRank& q = qs[i];
+    h2d_plan* p = q.p;
+    const h2d_tile_t& t = p->desc.tile;
+    if (!p->s_h2d) H2D_CUDA_TRY(cudaStreamCreateWithFlags(&p->s_h2d, cudaStreamNonBlocking));
+    if (!p->s_d2h) H2D_CUDA_TRY(cudaStreamCreateWithFlags(&p->s_d2h, cudaStreamNonBlocking));
+    cudaEvent_t e_start;
+    if (int rc = q.new_event(&e_start)) return rc;
+    H2D_CUDA_TRY(cudaEventRecord(e_start, cs));
+    H2D_CUDA_TRY(cudaStreamWaitEvent(p->s_h2d, e_start, 0));
+    H2D_CUDA_TRY(cudaStreamWaitEvent(p->s_d2h, e_start, 0));
+    q.up.assign((size_t)n_units, nullptr);
+  }
+  // unit-major, so that with several tiles in one process every tile's first rows arrive first
   for (int u = 0; u < n_units; ++u) {
     const int r0 = u * U, r1 = r0 + U < rows ? r0 + U : rows;
-    H2D_CUDA_TRY(cudaMemcpy2DAsync(dev_row(0, r0), (size_t)t.pitch * 4, host_in + (int64_t)r0 * in_pitch,
-                                   (size_t)in_pitch * 4, (size_t)t.cols * 4, (size_t)(r1 - r0),
-                                   cudaMemcpyHostToDevice, p->s_h2d));
-    if (int rc = new_event(&up[u])) return rc;
-    H2D_CUDA_TRY(cudaEventRecord(up[u], p->s_h2d));
+    for (int i = 0; i < n; ++i) {
+      PipeRank& q = qs[i];
+      const h2d_tile_t& t = q.p->desc.tile;
+      H2D_CUDA_TRY(cudaMemcpy2DAsync(q.dev_row(0, r0) + q.up_c0, (size_t)t.pitch * 4,
+                                     q.host_in + (int64_t)r0 * q.in_pitch + q.up_c0, (size_t)q.in_pitch * 4,
+                                     (size_t)q.up_w * 4, (size_t)(r1 - r0), cudaMemcpyHostToDevice, q.p->s_h2d));
+      if (int rc = q.new_event(&q.up[(size_t)u])) return rc;
+      H2D_CUDA_TRY(cudaEventRecord(q.up[(size_t)u], q.p->s_h2d));
+    }
   }
 
   const int out_par = L & 1;
-  int waited = -1;                                       // last upload unit the compute stream waits for
   const int64_t span = (int64_t)rows + (int64_t)S * (L > 0 ? L - 1 : 0);
   // block boundaries over [0, span): ramp up, plateau of M, ramp down
   std::vector<int64_t> bounds;
@@ -1315,55 +1444,93 @@ int h2d_plan_solve_pipelined(h2d_plan_t* p, const float* host_in, int64_t in_pit
     if (bounds.back() < span) bounds.push_back(span);
   }
   const int n_blocks = bounds.empty() ? 0 : (int)bounds.size() - 1;
-  int d2h_done_rows = 0;                                 // rows [0, d2h_done_rows) already queued for download
   for (int b = 0; b < n_blocks; ++b) {
     const int64_t b_lo = bounds[b], b_hi = bounds[b + 1];
     // level 0 of this block reads rows below b_hi + k
     int64_t need_row = b_hi + k;
     if (need_row > rows) need_row = rows;
     const int need_unit = (int)((need_row - 1) / U);
-    if (need_unit > waited) {
-      H2D_CUDA_TRY(cudaStreamWaitEvent(cs, up[need_unit], 0));
-      waited = need_unit;
-    }
+    for (int i = 0; i < n; ++i)
+      if (need_unit > qs[i].waited) {
+        H2D_CUDA_TRY(cudaStreamWaitEvent(cs, qs[i].up[(size_t)need_unit], 0));
+        qs[i].waited = need_unit;
+      }
     for (int e = 0; e < L; ++e) {
       int64_t lo = b_lo - (int64_t)S * e, hi = b_hi - (int64_t)S * e;
       if (hi <= 0 || lo >= rows) continue;
       if (lo < 0) lo = 0;
       if (hi > rows) hi = rows;
       const int kk = (e < L - 1) ? k : (int)(steps - (int64_t)(L - 1) * k);
-      if (int rc = launch_window(p, e & 1, kk, (int)lo, (int)hi, R, cs)) return rc;
+      for (int i = 0; i < n; ++i)
+        if (int rc = launch_window(qs[i].p, e & 1, kk, (int)lo, (int)hi, qs[i].R, cs, epoch)) return rc;
+      ++epoch;   // one epoch per issued window, on every rank alike
     }
     // rows below b_hi - S*(L-1) now hold the final field
     int64_t fin = b_hi - (int64_t)S * (L - 1);
     if (b == n_blocks - 1 || fin > rows) fin = rows;
-    if (fin > d2h_done_rows) {
+    for (int i = 0; i < n; ++i) {
+      PipeRank& q = qs[i];
+      if (fin <= q.d2h_done_rows) continue;
+      const h2d_tile_t& t = q.p->desc.tile;
       cudaEvent_t ev;
-      if (int rc = new_event(&ev)) return rc;
+      if (int rc = q.new_event(&ev)) return rc;
       H2D_CUDA_TRY(cudaEventRecord(ev, cs));
-      H2D_CUDA_TRY(cudaStreamWaitEvent(p->s_d2h, ev, 0));
-      H2D_CUDA_TRY(cudaMemcpy2DAsync(host_out + (int64_t)d2h_done_rows * out_pitch, (size_t)out_pitch * 4,
-                                     dev_row(out_par, d2h_done_rows), (size_t)t.pitch * 4, (size_t)t.cols * 4,
-                                     (size_t)(fin - d2h_done_rows), cudaMemcpyDeviceToHost, p->s_d2h));
-      d2h_done_rows = (int)fin;
+      H2D_CUDA_TRY(cudaStreamWaitEvent(q.p->s_d2h, ev, 0));
+      H2D_CUDA_TRY(cudaMemcpy2DAsync(q.host_out + (int64_t)q.d2h_done_rows * q.out_pitch, (size_t)q.out_pitch * 4,
+                                     q.dev_row(out_par, q.d2h_done_rows), (size_t)t.pitch * 4, (size_t)t.cols * 4,
+                                     (size_t)(fin - q.d2h_done_rows), cudaMemcpyDeviceToHost, q.p->s_d2h));
+      q.d2h_done_rows = (int)fin;
     }
   }
-  if (L == 0) {  // nothing to compute: upload, then download the same field
-    H2D_CUDA_TRY(cudaStreamWaitEvent(p->s_d2h, up[n_units - 1], 0));
-    H2D_CUDA_TRY(cudaMemcpy2DAsync(host_out, (size_t)out_pitch * 4, dev_row(0, 0), (size_t)t.pitch * 4,
-                                   (size_t)t.cols * 4, (size_t)rows, cudaMemcpyDeviceToHost, p->s_d2h));
+  for (int i = 0; i < n; ++i) {
+    PipeRank& q = qs[i];
+    const h2d_tile_t& t = q.p->desc.tile;
+    if (L == 0) {  // nothing to compute: upload, then download the same field
+      H2D_CUDA_TRY(cudaStreamWaitEvent(q.p->s_d2h, q.up[(size_t)n_units - 1], 0));
+      H2D_CUDA_TRY(cudaMemcpy2DAsync(q.host_out, (size_t)q.out_pitch * 4, q.dev_row(0, 0), (size_t)t.pitch * 4,
+                                     (size_t)t.cols * 4, (size_t)rows, cudaMemcpyDeviceToHost, q.p->s_d2h));
+    }
+    // the caller's stream completes when the last download (and upload) has
+    cudaEvent_t e_end;
+    if (int rc = q.new_event(&e_end)) return rc;
+    H2D_CUDA_TRY(cudaEventRecord(e_end, q.p->s_d2h));
+    H2D_CUDA_TRY(cudaStreamWaitEvent(cs, e_end, 0));
+    cudaEvent_t e_end2;
+    if (int rc = q.new_event(&e_end2)) return rc;
+    H2D_CUDA_TRY(cudaEventRecord(e_end2, q.p->s_h2d));
+    H2D_CUDA_TRY(cudaStreamWaitEvent(cs, e_end2, 0));
   }
-  // the caller's stream completes when the last download has
-  cudaEvent_t e_end;
-  if (int rc = new_event(&e_end)) return rc;
-  H2D_CUDA_TRY(cudaEventRecord(e_end, p->s_d2h));
-  H2D_CUDA_TRY(cudaStreamWaitEvent(cs, e_end, 0));
-  cudaEvent_t e_end2;
-  if (int rc = new_event(&e_end2)) return rc;
-  H2D_CUDA_TRY(cudaEventRecord(e_end2, p->s_h2d));
-  H2D_CUDA_TRY(cudaStreamWaitEvent(cs, e_end2, 0));
   if (final_parity) *final_parity = out_par;
+  if (epochs_used) *epochs_used = epoch - epoch0;
   return H2D_OK;
+}
+
+int h2d_plan_solve_pipelined_ex(h2d_plan_t* p, const float* host_in, int64_t in_pitch, float* host_out,
+                                int64_t out_pitch, int64_t steps, int k, int block_rows, int skew_rows,
+                                int wave_rows, uint32_t epoch0, void* stream, int* final_parity,
+                                uint32_t* epochs_used) {
+  PipeRank q;
+  q.p = p; q.host_in = host_in; q.host_out = host_out; q.in_pitch = in_pitch; q.out_pitch = out_pitch;
+  return pipelined_solve(&q, 1, steps, k, block_rows, skew_rows, wave_rows, epoch0, (cudaStream_t)stream,
+                         final_parity, epochs_used);
+}
+
+int h2d_plan_solve_pipelined_many(h2d_plan_t* const* plans, int n_plans, const float* const* host_in,
+                                  const int64_t* in_pitch, float* const* host_out, const int64_t* out_pitch,
+                                  int64_t steps, int k, int block_rows, int skew_rows, uint32_t epoch0,
+                                  void* stream, int* final_parity, uint32_t* epochs_used) {
+  if (!plans || n_plans < 1 || !host_in || !in_pitch || !host_out || !out_pitch)
+    return h2d_fail(H2D_EINVAL, "h2d_plan_solve_pipelined_many: bad argument");
+  std::vector<PipeRank> qs((size_t)n_plans);
+  for (int i = 0; i < n_plans; ++i) {
+    qs[(size_t)i].p = plans[i];
+    qs[(size_t)i].host_in = host_in[i];
+    qs[(size_t)i].host_out = host_out[i];
+    qs[(size_t)i].in_pitch = in_pitch[i];
+    qs[(size_t)i].out_pitch = out_pitch[i];
+  }
+  return pipelined_solve(qs.data(), n_plans, steps, k, block_rows, skew_rows, 0, epoch0, (cudaStream_t)stream,
+                         final_parity, epochs_used);
 }
 
 int64_t h2d_plan_launch_count(const h2d_plan_t* p) { return p ? p->launches : 0; }

@@ -122,6 +122,16 @@ def cuda():
             lib.h2d_cuda_step_k1.argtypes = [vp, vp, P(Tile), P(Phys), vp]
             lib.h2d_plan_scratch_bytes.argtypes = [P(Tile), C.c_int32, C.c_int32]
             lib.h2d_plan_scratch_bytes.restype = C.c_size_t
+            lib.h2d_plan_solve_pipelined_ex.argtypes = [vp, vp, C.c_int64, vp, C.c_int64, C.c_int64, C.c_int, C.c_int,
+                                                        C.c_int, C.c_int, C.c_uint32, vp, P(C.c_int),
+                                                        P(C.c_uint32)]
+            lib.h2d_plan_solve_pipelined_ex.restype = C.c_int
+            lib.h2d_plan_solve_pipelined_many.argtypes = [P(vp), C.c_int, P(vp), P(C.c_int64), P(vp), P(C.c_int64),
+                                                          C.c_int64, C.c_int, C.c_int, C.c_int, C.c_uint32, vp,
+                                                          P(C.c_int), P(C.c_uint32)]
+            lib.h2d_plan_solve_pipelined_many.restype = C.c_int
+            lib.h2d_plan_wave_rows.argtypes = [vp]
+            lib.h2d_plan_wave_rows.restype = C.c_int32
             lib.h2d_plan_run_dataflow.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
             lib.h2d_plan_run_dataflow.restype = C.c_int
             lib.h2d_plan_chunk_rows.argtypes = [P(Tile), C.c_int32, C.c_int32]

@@ -387,10 +387,29 @@ class Heat2DSolver:
         (one tile, no convergence test).  `elapsed_s` covers all three."""
         cfg = self.cfg
         steps = cfg.steps if steps is None else steps
-        if len(self.engines) != 1 or self.world != 1 or cfg.backend not in ("fused", "single"):
-            raise ValueError("solve_pipelined needs the fused backend on a single tile")
         if cfg.conv:
             raise ValueError("solve_pipelined has no convergence test; use run()")
+        if len(self.engines) > 1 and cfg.px == 1 and cfg.backend == "fused":
+            # 1 x P virtual tiles: every window is issued for every tile in turn; host_in / host_out
+            # are the whole fields and each tile reads its ghost columns straight from host_in
+            plans = [e.plan for e in self.engines]
+            l0 = self.kernel_launches
+            ev0 = torch.cuda.Event(enable_timing=True)
+            ev1 = torch.cuda.Event(enable_timing=True)
+            with torch.cuda.device(self.device):
+                ev0.record()
+                self.parity, used = K.Plan.solve_pipelined_many(
+                    plans, host_in, host_out, [f.tile.y0 for f in self.fields], steps, cfg.k, self.epoch + 1,
+                    block_rows, skew_rows)
+                ev1.record()
+                ev1.synchronize()
+            self.epoch += used
+            self.steps_done = cfg.start_step + steps
+            self._check_faults()
+            return RunResult(self.steps_done, self.steps_done, False, float("nan"), ev0.elapsed_time(ev1) / 1e3,
+                             self.kernel_launches - l0, 0, cfg.nx, cfg.ny, steps)
+        if len(self.engines) != 1 or self.world != 1 or cfg.backend not in ("fused", "single"):
+            raise ValueError("solve_pipelined needs the fused backend on a single tile or a 1 x P grid")
         plan = self.engines[0].plan
         l0 = plan.launch_count
         ev0 = torch.cuda.Event(enable_timing=True)

@@ -246,6 +246,58 @@ class Plan:
                 int(steps), int(k), int(block_rows), int(skew_rows), _stream_ptr(self.device), C.byref(par)))
         return par.value
 
+    @staticmethod
+    def solve_pipelined_many(plans, host_in: torch.Tensor, host_out: torch.Tensor, col0s, steps: int, k: int,
+                             epoch0: int, block_rows: int = 0, skew_rows: int = 0):
+        """The pipelined solve for the tiles of a 1 x P grid emulated in one process: `host_in` /
+        `host_out` are the WHOLE pinned nx x ny fields, tile i owns columns col0s[i] .. +cols (its
+        ghost columns are simply the neighbouring columns of host_in).  Returns (parity, epochs)."""
+        for t_, nm in ((host_in, "host_in"), (host_out, "host_out")):
+            if t_.is_cuda or t_.dtype != torch.float32 or t_.dim() != 2 or t_.stride(1) != 1 or not t_.is_pinned():
+                raise ValueError(f"{nm} must be a pinned 2-D float32 host tensor with unit column stride")
+        n = len(plans)
+        lib = plans[0]._lib
+        arr = (C.c_void_p * n)(*[p._h for p in plans])
+        pin = (C.c_void_p * n)(*[host_in.data_ptr() + 4 * int(c) for c in col0s])
+        pout = (C.c_void_p * n)(*[host_out.data_ptr() + 4 * int(c) for c in col0s])
+        ipitch = (C.c_int64 * n)(*([host_in.stride(0)] * n))
+        opitch = (C.c_int64 * n)(*([host_out.stride(0)] * n))
+        par, used = C.c_int(0), C.c_uint32(0)
+        with torch.cuda.device(plans[0].device):
+            N.check(lib, lib.h2d_plan_solve_pipelined_many(arr, n, pin, ipitch, pout, opitch, int(steps), int(k),
+                                                           int(block_rows), int(skew_rows), epoch0 & 0xFFFFFFFF,
+                                                           _stream_ptr(plans[0].device), C.byref(par),
+                                                           C.byref(used)))
+        return par.value, int(used.value)
+
+    @property
+    def wave_rows(self) -> int:
+        """Rows one wave of window tasks covers (block granularity of the pipelined solve)."""
+        return int(self._lib.h2d_plan_wave_rows(self._h))
+
+    def solve_pipelined_strip(self, host_in: torch.Tensor, col0: int, host_out: torch.Tensor, steps: int, k: int,
+                              epoch0: int, wave_rows: int, block_rows: int = 0, skew_rows: int = 0):
+        """Pipelined upload / solve / download for one rank of a 1 x P column-strip run
+        (h2d_plan_solve_pipelined_ex).  `host_in`: pinned (rows, >= col0 + cols + margin) tensor
+        whose column `col0` is owned column 0 and which holds 32 valid ghost columns on each side
+        that has a neighbour; `host_out`: pinned (rows, cols).  Returns (parity, epochs used)."""
+        for t_, nm in ((host_in, "host_in"), (host_out, "host_out")):
+            if t_.is_cuda or t_.dtype != torch.float32 or t_.dim() != 2 or t_.stride(1) != 1:
+                raise ValueError(f"{nm} must be a 2-D float32 host tensor with unit column stride")
+            if not t_.is_pinned():
+                raise ValueError(f"{nm} must be pinned (torch.Tensor.pin_memory) for the copies to overlap")
+        if host_in.shape[0] != self.tile.rows or tuple(host_out.shape) != (self.tile.rows, self.tile.cols):
+            raise ValueError("host_in / host_out do not match the tile")
+        if col0 < 0 or col0 + self.tile.cols > host_in.shape[1]:
+            raise ValueError("col0 + cols exceeds host_in")
+        par, used = C.c_int(0), C.c_uint32(0)
+        with torch.cuda.device(self.device):
+            N.check(self._lib, self._lib.h2d_plan_solve_pipelined_ex(
+                self._h, host_in.data_ptr() + 4 * col0, host_in.stride(0), host_out.data_ptr(), host_out.stride(0),
+                int(steps), int(k), int(block_rows), int(skew_rows), int(wave_rows), epoch0 & 0xFFFFFFFF,
+                _stream_ptr(self.device), C.byref(par), C.byref(used)))
+        return par.value, int(used.value)
+
     @property
     def launch_count(self) -> int:
         return int(self._lib.h2d_plan_launch_count(self._h))

@@ -206,6 +206,54 @@ class DistributedHeat2DSolver(Heat2DSolver):
             res.elapsed_s = float(t.item())
         return res
 
+    GHOST_COLS = 32   # ghost columns the pipelined solve uploads per side (TK_WE_COLS)
+
+    def host_strip(self, pinned: bool = True):
+        """(host_in, col0, host_out) for `solve_pipelined`: a (rows, cols + ghosts) input whose
+        column `col0` is this rank's owned column 0, and a (rows, cols) output."""
+        spec = self.decomp.tile(self.rank)
+        gw = self.GHOST_COLS if spec.neighbours["W"] is not None else 0
+        ge = self.GHOST_COLS if spec.neighbours["E"] is not None else 0
+        hin = torch.zeros((spec.rows, gw + spec.cols + ge), dtype=torch.float32, pin_memory=pinned)
+        hout = torch.empty((spec.rows, spec.cols), dtype=torch.float32, pin_memory=pinned)
+        return hin, gw, hout
+
+    def solve_pipelined(self, host_in: torch.Tensor, col0: int, host_out: torch.Tensor,
+                        steps: Optional[int] = None) -> RunResult:
+        """End to end on a 1 x P process grid: every rank uploads its column strip (plus the
+        ghost columns of the initial field), advances `steps` steps and downloads its result, the
+        three phases overlapped block by block and the ranks in lockstep (see
+        h2d_plan_solve_pipelined_ex).  `elapsed_s` = device time of the slowest rank."""
+        cfg = self.cfg
+        steps = cfg.steps if steps is None else steps
+        if cfg.px != 1:
+            raise ValueError("solve_pipelined needs column strips (px = 1): row strips serialise the ranks")
+        if cfg.conv:
+            raise ValueError("solve_pipelined has no convergence test; use run()")
+        plan = self.engines[0].plan
+        wave = torch.tensor([plan.wave_rows], dtype=torch.int64, device=self.device)
+        if self._wsize > 1:
+            dist.all_reduce(wave, op=dist.ReduceOp.MIN)
+        l0 = plan.launch_count
+        self.barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.device(self.device):
+            ev0.record()
+            self.parity, used = plan.solve_pipelined_strip(host_in, col0, host_out, steps, cfg.k, self.epoch + 1,
+                                                           int(wave.item()))
+            ev1.record()
+            ev1.synchronize()
+        self.epoch += used
+        self.steps_done = cfg.start_step + steps
+        el = ev0.elapsed_time(ev1) / 1e3
+        if self._wsize > 1:
+            t = torch.tensor([el], dtype=torch.float64, device=self.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            el = float(t.item())
+        self._check_faults()
+        return RunResult(self.steps_done, self.steps_done, False, float("nan"), el, plan.launch_count - l0, 0,
+                         cfg.nx, cfg.ny, steps)
+
     def gather(self, out: Optional[torch.Tensor] = None, dst: int = 0) -> Optional[torch.Tensor]:
         """Assemble the global field on rank `dst` (device copies over NCCL)."""
         cfg = self.cfg

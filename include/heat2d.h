@@ -253,6 +253,30 @@ int h2d_plan_solve_pipelined(h2d_plan_t* plan, const float* host_in, int64_t in_
                              int64_t out_pitch, int64_t steps, int k, int block_rows, int skew_rows,
                              void* stream, int* final_parity);
 
+/* The same for a rank of a 1 x P column-strip run (plans whose only neighbours are W and E):
+ * every rank owns all rows, cuts the same row blocks and issues the same sequence of window
+ * launches — one epoch each, starting at epoch0; *epochs_used tells the caller how far the
+ * shared epoch counter advanced — so the column bands and flags travel per window exactly as
+ * they do per whole-tile launch.  `wave_rows` (> 0) fixes the block granularity; ranks must
+ * pass the same value (the minimum of h2d_plan_wave_rows over the ranks).  host_in points
+ * at owned cell (0,0) of this rank's strip inside a host array that also holds 32 valid
+ * columns to the left / right of it wherever a W / E neighbour exists (the level-0 ghosts).
+ * Row strips cannot be pipelined this way (a strip's top halo is produced by the last block
+ * of the strip above), so the call refuses N / S neighbours.                                */
+int h2d_plan_solve_pipelined_ex(h2d_plan_t* plan, const float* host_in, int64_t in_pitch, float* host_out,
+                                int64_t out_pitch, int64_t steps, int k, int block_rows, int skew_rows,
+                                int wave_rows, uint32_t epoch0, void* stream, int* final_parity,
+                                uint32_t* epochs_used);
+/* The tiles of a 1 x P grid emulated in ONE process (several plans, one compute stream):
+ * every window launch is issued for every plan before the next one.  Arrays have one entry
+ * per plan; the block granularity is the minimum over the plans.                          */
+int h2d_plan_solve_pipelined_many(h2d_plan_t* const* plans, int n_plans, const float* const* host_in,
+                                  const int64_t* in_pitch, float* const* host_out, const int64_t* out_pitch,
+                                  int64_t steps, int k, int block_rows, int skew_rows, uint32_t epoch0,
+                                  void* stream, int* final_parity, uint32_t* epochs_used);
+/* Rows that one wave of window tasks covers for this plan (block granularity above). */
+int32_t h2d_plan_wave_rows(const h2d_plan_t* plan);
+
 /* Number of kernels launched by this plan since creation (bench bookkeeping). */
 int64_t h2d_plan_launch_count(const h2d_plan_t* plan);
 /* Device address of this rank's partial norm (1 float, valid after a launch

@@ -29,8 +29,31 @@ def main():
         else:
             u0 = K.cpu_initial_grid(cfg.nx, cfg.ny, cfg.init)
             s.initialize()
-        res = s.run()
-        out = s.gather()
+        if case.get("pipelined"):
+            # column strips, end to end from / to pinned host memory, ranks in lockstep
+            hin, col0, hout = s.host_strip()
+            spec_t = s.decomp.tile(rank)
+            c_lo, c_hi = spec_t.y0 - col0, spec_t.y0 + spec_t.cols + (hin.shape[1] - col0 - spec_t.cols)
+            hin.copy_(torch.from_numpy(np.ascontiguousarray(u0[:, c_lo:c_hi])))
+            res = s.solve_pipelined(hin, col0, hout)
+            # a run() afterwards must find flags and epochs in a consistent state
+            res2 = s.run(cfg.k)
+            parts = [None] * world
+            dist.all_gather_object(parts, (spec_t.y0, spec_t.cols, hout.numpy().copy()))
+            out = torch.empty((cfg.nx, cfg.ny), dtype=torch.float32)
+            for y0, cols, part in parts:
+                out[:, y0:y0 + cols] = torch.from_numpy(part)
+            after = s.gather()
+            if rank == 0:
+                ref2 = u0.copy()
+                K.cpu_run(ref2, cfg.steps + cfg.k, N.make_phys(cfg.cx_eff, cfg.cy_eff, cfg.boundary, cfg.arith),
+                          "none", 20, 0.1, threads=8)
+                if not np.array_equal(after.numpy(), ref2) or res2.steps_done != cfg.steps + cfg.k:
+                    ok_all = False
+                    results.append({"name": case.get("name", "") + " (run after pipelined)", "ok": False})
+        else:
+            res = s.run()
+            out = s.gather()
         if rank == 0:
             ref = u0.copy()
             done, last = K.cpu_run(ref, cfg.steps, N.make_phys(cfg.cx_eff, cfg.cy_eff, cfg.boundary, cfg.arith),

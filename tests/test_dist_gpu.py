@@ -85,3 +85,22 @@ def test_flag_protocol_under_injected_delays():
               "cfg": dict(nx=768, ny=1024, px=px, py=py, k=8, steps=120, backend="fused", chunk_rows=32)}]
     out = _run(px * py, {"cases": cases}, env_extra={"H2D_DEBUG_DELAY": "1"})
     assert out["ok"], out
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+@pytest.mark.skipif(os.environ.get("H2D_EXPERIMENTAL") != "1",
+                    reason="validated on one GPU with virtual tiles (test_gpu_kernels.py); the one-process-per-GPU "
+                           "form has not run on multi-GPU hardware yet: set H2D_EXPERIMENTAL=1")
+@pytest.mark.parametrize("delay", [False, True])
+def test_pipelined_solve_on_column_strips(delay):
+    """End to end on a 1 x P grid: upload / window launches with W-E halo exchange / download,
+    all ranks cutting the same row blocks; then an ordinary run() on the same solver."""
+    n = min(_ngpu(), 4)
+    cases = [
+        {"name": "pipelined-k8", "random": True, "pipelined": True,
+         "cfg": dict(nx=3000, ny=256 * n, px=1, py=n, k=8, steps=83, backend="fused", chunk_rows=64)},
+        {"name": "pipelined-k5-ring", "random": True, "pipelined": True,
+         "cfg": dict(nx=1500, ny=192 * n, px=1, py=n, k=5, steps=41, backend="fused", boundary="ghost-ring")},
+    ]
+    out = _run(n, {"cases": cases}, env_extra={"H2D_DEBUG_DELAY": "1"} if delay else None)
+    assert out["ok"], out

@@ -345,3 +345,21 @@ def test_solve_api_uses_the_pipelined_path_for_pinned_input():
     assert np.array_equal(field.numpy(), oracle(nx, ny, 30, u0=u0))
     res2, field2 = solve(HeatConfig(nx=nx, ny=ny, steps=30, k=8), u0=u0)      # ordinary path, numpy in
     assert np.array_equal(field2.numpy(), field.numpy())
+
+
+@pytest.mark.parametrize("py,shape,steps,k,block", [(2, (1500, 512), 83, 8, 0), (3, (900, 768), 41, 5, 128),
+                                                    (4, (2200, 1024), 24, 8, 256)])
+def test_pipelined_solve_on_virtual_column_strips(py, shape, steps, k, block):
+    """1 x P tiles in one process: upload / window launches with W-E halo exchange / download,
+    then an ordinary run() from the state it left (flags, epochs, ghost margins)."""
+    nx, ny = shape
+    u0 = rand_grid(nx, ny, py)
+    hin = torch.from_numpy(u0).pin_memory()
+    hout = torch.empty((nx, ny), dtype=torch.float32).pin_memory()
+    s = Heat2DSolver(HeatConfig(nx=nx, ny=ny, steps=steps, k=k, px=1, py=py, chunk_rows=48), DEV)
+    res = s.solve_pipelined(hin, hout, block_rows=block)
+    torch.cuda.synchronize()
+    assert res.steps_done == steps
+    assert np.array_equal(hout.numpy(), oracle(nx, ny, steps, u0=u0))
+    s.run(2 * k + 1)
+    assert np.array_equal(s.gather().numpy(), oracle(nx, ny, steps + 2 * k + 1, u0=u0))
