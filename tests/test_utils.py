@@ -78,3 +78,26 @@ def test_phase_timer_accumulates_and_nvtx_is_free_without_cuda(monkeypatch):
         pass
     d = t.as_dict()
     assert d["wall_s"]["a"] >= 0.02 and "b" in d["wall_s"] and d["device_s"] == {}
+
+
+def test_lazy_module_imports_on_first_use():
+    import sys
+    from heat2d_b200._lazy import LazyModule
+    sys.modules.pop("colorsys", None)
+    m = LazyModule("colorsys")
+    assert "not loaded" in repr(m) and "colorsys" not in sys.modules
+    assert m.rgb_to_hsv(1.0, 0.0, 0.0)[0] == 0.0
+    assert "colorsys" in sys.modules and "(loaded)" in repr(m)
+
+
+def test_build_uses_shipped_libraries_when_sources_are_absent(tmp_path):
+    """An installed copy has the .so files but no csrc/: they must be used as they are."""
+    from heat2d_b200 import build as B
+    lib = tmp_path / "lib.so"
+    lib.write_bytes(b"x")
+    assert B._newer(lib, [tmp_path / "missing.cpp"])          # no sources -> up to date
+    src = tmp_path / "a.cpp"
+    src.write_text("int x;")
+    os.utime(lib, (1, 1))
+    assert not B._newer(lib, [src])                            # a newer source -> rebuild
+    assert not B._newer(tmp_path / "absent.so", [src])
