@@ -1264,9 +1264,21 @@ int h2d_plan_run_dataflow(h2d_plan_t* p, int src_parity, int k, int n_epochs, vo
 
 // Rows of one wave of window tasks for this plan (see h2d_plan_solve_pipelined): ranks of a
 // column-strip run agree on the minimum of this value so that they cut the same blocks.
+// Tuning hooks of the pipelined solve (sweeps without rebuilding; defaults unchanged):
+// H2D_PIPE_CHUNK_MAX = largest chunk (default 384 rows), H2D_PIPE_BLOCK_WAVES = waves of
+// tasks per plateau block (default 4).
+static int env_int(const char* name, int lo, int hi, int dflt) {
+  const char* e = getenv(name);
+  if (e && e[0]) {
+    const int v = atoi(e);
+    if (v >= lo && v <= hi) return v;
+  }
+  return dflt;
+}
 static int pipelined_chunk_rows(const h2d_plan* p) {
+  const int cap = env_int("H2D_PIPE_CHUNK_MAX", 16, 1 << 20, 384);
   int R = p->chunk_rows;
-  while (R > 384) R = (R + 1) / 2;
+  while (R > cap) R = (R + 1) / 2;
   return R;
 }
 static int pipelined_wave_rows(const h2d_plan* p) {
@@ -1381,7 +1393,7 @@ static int pipelined_solve(PipeRank* qs, int n, int64_t steps, int k, int block_
       if (w < M1) M1 = w;
     }
   }
-  int M = block_rows > 0 ? block_rows : 4 * M1;
+  int M = block_rows > 0 ? block_rows : env_int("H2D_PIPE_BLOCK_WAVES", 1, 64, 4) * M1;
   // Narrow tiles (column strips on many GPUs: 37 task strips at 4096 columns) reach one wave
   // of tasks only with thousands of rows; keep at least ~4 blocks so that upload, compute and
   // download still overlap, but never less than one full wave per window.
