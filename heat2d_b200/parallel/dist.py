@@ -372,6 +372,53 @@ class HaloExchangeSolver:
                 else:
                     src[hr:hr + t.rows, hc + t.cols] = self._recv[d]
 
+    # ---- CPU path with the reference's overlap (grad1612_mpi_heat.c:233-259): start the halo
+    # transfers, sweep the cells that need no ghost, wait, sweep the edge ring.
+    def _sub_step(self, i0: int, i1: int, j0: int, j1: int):
+        """One step on owned cells [i0, i1) x [j0, j1) of the tile (CPU arrays)."""
+        if i1 <= i0 or j1 <= j0:
+            return
+        f, t = self.field, self.field.tile
+        sub = N.Tile(t.nx, t.ny, t.x0 + i0, t.y0 + j0, i1 - i0, j1 - j0, t.halo_r, t.halo_c, t.pitch)
+        off = i0 * t.pitch + j0
+        src = f.buf[self.parity].numpy().reshape(-1)[off:]
+        dst = f.buf[1 - self.parity].numpy().reshape(-1)[off:]
+        K.cpu_step_tile(src, dst, sub, self.phys)
+
+    def _exchange_and_step_overlapped(self):
+        f, t = self.field, self.field.tile
+        nbs = self.spec.neighbours
+        o = f.owned(self.parity)
+        ops = []
+        for d in "NSWE":
+            if nbs[d] is None:
+                continue
+            edge = {"N": o[0, :], "S": o[-1, :], "W": o[:, 0], "E": o[:, -1]}[d]
+            self._send[d].copy_(edge)
+            ops.append(dist.P2POp(dist.isend, self._send[d], nbs[d]))
+            ops.append(dist.P2POp(dist.irecv, self._recv[d], nbs[d]))
+        works = dist.batch_isend_irecv(ops) if ops else []
+        self._sub_step(1, t.rows - 1, 1, t.cols - 1)            # interior: no ghost needed
+        for w in works:
+            w.wait()
+        src = f.buf[self.parity]
+        hr, hc = t.halo_r, t.halo_c
+        for d in "NSWE":
+            if nbs[d] is None:
+                continue
+            if d == "N":
+                src[hr - 1, hc:hc + t.cols] = self._recv[d]
+            elif d == "S":
+                src[hr + t.rows, hc:hc + t.cols] = self._recv[d]
+            elif d == "W":
+                src[hr:hr + t.rows, hc - 1] = self._recv[d]
+            else:
+                src[hr:hr + t.rows, hc + t.cols] = self._recv[d]
+        self._sub_step(0, 1, 0, t.cols)                         # edge rows ...
+        self._sub_step(t.rows - 1, t.rows, 0, t.cols)
+        self._sub_step(1, t.rows - 1, 0, 1)                     # ... and edge columns
+        self._sub_step(1, t.rows - 1, t.cols - 1, t.cols)
+
     def _step(self):
         f = self.field
         if self.on_gpu:
@@ -407,9 +454,13 @@ class HaloExchangeSolver:
         converged, last, checks, iterations = False, float("nan"), 0, None
         done0 = self.steps_done
         for s in range(self.steps_done, self.steps_done + steps):
-            if self.world > 1:
-                self._exchange()
-            self._step()
+            t_ = self.field.tile
+            if self.world > 1 and not self.on_gpu and t_.rows >= 3 and t_.cols >= 3:
+                self._exchange_and_step_overlapped()
+            else:
+                if self.world > 1:
+                    self._exchange()
+                self._step()
             if cfg.conv and s % cfg.interval == 0:
                 last = self._norm()
                 checks += 1
