@@ -137,25 +137,25 @@ def make_schedule(steps: int, k: int, conv: bool = False, interval: int = 20,
     out = []
     s = start_step
     end = start_step + steps
-    while s < end:
-        if not conv:
-            kk = min(k, end - s)
-            out.append(Launch(kk, False, s))
-            s += kk
-            continue
-        nxt = ((s + interval - 1) // interval) * interval  # next checked index >= s
-        if nxt >= end:
-            kk = min(k, end - s)
-            out.append(Launch(kk, False, s))
-            s += kk
-            continue
-        n = nxt - s + 1  # steps up to and including the checked one: the last launch ends on it
+
+    def stretch(n: int, check_last: bool):
         # as few launches as k allows, of (nearly) equal depth: 20 steps at k = 8 -> 7 + 7 + 6,
         # not 8 + 8 + 4 (a shallow launch is HBM-bound, a deep one is not)
+        nonlocal s
         parts = -(-n // k)
         base, extra = divmod(n, parts)
         for i in range(parts):
             kk = base + (1 if i < extra else 0)
-            out.append(Launch(kk, i == parts - 1, s))
+            out.append(Launch(kk, check_last and i == parts - 1, s))
             s += kk
+
+    while s < end:
+        if not conv:
+            stretch(end - s, False)
+            continue
+        nxt = ((s + interval - 1) // interval) * interval  # next checked index >= s
+        if nxt >= end:
+            stretch(end - s, False)
+            continue
+        stretch(nxt - s + 1, True)  # up to and including the checked step: the last launch ends on it
     return out

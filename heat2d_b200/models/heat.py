@@ -168,6 +168,23 @@ class TileEngine:
                 self.ctl.data_ptr(), phase, int(self.spin_timeout_s * 1e9), self.plan.fault_ptr,
                 int(torch.cuda.current_stream(dev).cuda_stream)))
 
+    def device_barrier(self, seq: int):
+        """Queue a one-block kernel that returns only after EVERY rank's stream has reached
+        the same point (the all-to-all of the norm finish with a threshold nothing meets).
+        It aligns the start of a timed region across GPUs to a few microseconds, where a host
+        barrier leaves the ranks' launch skew inside the window (MPI_Barrier before
+        MPI_Wtime, grad1612_mpi_heat.c:206-207)."""
+        lib = N.cuda()
+        dev = self.field.device
+        if not hasattr(self, "_bar_stop"):
+            self._bar_stop = torch.zeros(1, dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            N.check(lib, lib.h2d_cuda_norm_finish(
+                self.plan.norm_ptr, self.vals_ptrs.data_ptr(), self.flags_ptrs.data_ptr(), self.rank,
+                self.world, seq & 0xFFFFFFFF, N.NORM["linf"], float("-inf"), self.norm_total.data_ptr(),
+                self._bar_stop.data_ptr(), 2, int(self.spin_timeout_s * 1e9), self.plan.fault_ptr,
+                int(torch.cuda.current_stream(dev).cuda_stream)))
+
     def fault(self) -> int:
         return int(self._fault.item())
 

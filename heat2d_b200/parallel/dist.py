@@ -196,8 +196,17 @@ class DistributedHeat2DSolver(Heat2DSolver):
         self.barrier()
         return self
 
+    def device_barrier(self):
+        """Align the ranks' streams on the device (see TileEngine.device_barrier)."""
+        if self._wsize > 1:
+            self.norm_seq += 1
+            self.engines[0].device_barrier(self.norm_seq)
+
     def run(self, steps: Optional[int] = None) -> RunResult:
         self.barrier()
+        # the host barrier leaves tens of microseconds of launch skew between the ranks; the
+        # device-side one puts every rank's start event within the NVLink latency of the others
+        self.device_barrier()
         res = super().run(steps)
         if self._wsize > 1:
             # elapsed = max over ranks (MPI_Reduce(MAX), grad1612_mpi_heat.c:280)

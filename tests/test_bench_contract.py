@@ -48,3 +48,35 @@ def test_configure_rewrites_only_the_requested_defines():
     changed = [(x, y) for x, y in zip(a, b) if x != y]
     assert len(changed) == 3 and all(x.startswith("#define") and y.startswith("#define") for x, y in changed)
     assert any("123" in y for _, y in changed) and any("456" in y for _, y in changed)
+
+
+def _bench_module():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("h2d_bench", os.path.join(ROOT, "bench.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+def test_both_arms_print_the_same_metric_and_an_e2e_block():
+    """The driver divides the repo arm by the reference arm only when metric, unit and
+    direction agree, and computes the end-to-end ratio only when both arms carry `e2e`
+    (round 1 lost both ratios to a metric string that differed by three words)."""
+    import inspect
+    b = _bench_module()
+    ref_src = inspect.getsource(b.reference_arm)
+    main_src = inspect.getsource(b.main)
+    assert '"metric": METRIC' in ref_src and '"metric": METRIC' in main_src
+    assert ref_src.count('"metric"') == 1 and '"unit": "GLUP/s"' in ref_src and '"unit": "GLUP/s"' in main_src
+    assert '"higher_is_better": True' in ref_src and '"higher_is_better": True' in main_src
+    assert '"e2e"' in ref_src and '"h2d_bytes_per_step"' in ref_src and '"d2h_bytes_per_step"' in ref_src
+    assert 'out["e2e"] = e2e' in main_src
+    # the like-for-like number and the verification flag are part of the record
+    assert '"same_arith"' in main_src and '"verified"' in main_src
+
+
+def test_headline_arithmetic_is_the_reference_arithmetic():
+    b = _bench_module()
+    a = b.parse_args([])
+    assert a.arith == "strict-fma" and a.gpus == 1
+    assert b.parse_args(["--arith", "fp32"]).arith == "fp32"

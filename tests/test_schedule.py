@@ -6,8 +6,10 @@ from heat2d_b200.config import ConfigError, HeatConfig, make_schedule
 def test_plain_schedule():
     s = make_schedule(1000, 8)
     assert sum(l.k for l in s) == 1000 and len(s) == 125 and not any(l.check for l in s)
-    s = make_schedule(10, 8)
-    assert [l.k for l in s] == [8, 2]
+    # never a trailing shallow launch: equal depths, as few launches as k allows
+    assert [l.k for l in make_schedule(10, 8)] == [5, 5]
+    assert [l.k for l in make_schedule(20, 8)] == [7, 7, 6]
+    assert [l.k for l in make_schedule(5, 8)] == [5]
     assert make_schedule(0, 8) == []
 
 
