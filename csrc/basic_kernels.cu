@@ -131,7 +131,7 @@ norm_diff_kernel(const float* __restrict__ a, const float* __restrict__ b, Geo g
     const int64_t off = (int64_t)(i + g.halo_r) * g.pitch + g.halo_c;
     for (int j = threadIdx.x; j < g.cols; j += NORM_THREADS) {
       const float d = a[off + j] - b[off + j];
-      acc = (norm == H2D_NORM_L2SQ) ? fmaf(d, d, acc) : fmaxf(acc, fabsf(d));
+      acc = (norm == H2D_NORM_L2SQ) ? fmaf(d, d, acc) : fmax_nan(acc, fabsf(d));
     }
   }
   acc = (norm == H2D_NORM_L2SQ) ? warp_sum(acc) : warp_max(acc);
@@ -140,7 +140,7 @@ norm_diff_kernel(const float* __restrict__ a, const float* __restrict__ b, Geo g
   if (threadIdx.x == 0) {
     float v = red[0];
     for (int w = 1; w < NORM_THREADS / 32; ++w)
-      v = (norm == H2D_NORM_L2SQ) ? v + red[w] : fmaxf(v, red[w]);
+      v = (norm == H2D_NORM_L2SQ) ? v + red[w] : fmax_nan(v, red[w]);
     partials[blockIdx.x] = v;
     __threadfence();
     const unsigned prev = atomicAdd(counter, 1u);
@@ -152,7 +152,7 @@ norm_diff_kernel(const float* __restrict__ a, const float* __restrict__ b, Geo g
   float v = 0.f;
   for (int i = threadIdx.x; i < (int)gridDim.x; i += NORM_THREADS) {
     const float x = __ldcg(partials + i);
-    v = (norm == H2D_NORM_L2SQ) ? v + x : fmaxf(v, x);
+    v = (norm == H2D_NORM_L2SQ) ? v + x : fmax_nan(v, x);
   }
   v = (norm == H2D_NORM_L2SQ) ? warp_sum(v) : warp_max(v);
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
@@ -160,7 +160,7 @@ norm_diff_kernel(const float* __restrict__ a, const float* __restrict__ b, Geo g
   if (threadIdx.x == 0) {
     float t = red[0];
     for (int w = 1; w < NORM_THREADS / 32; ++w)
-      t = (norm == H2D_NORM_L2SQ) ? t + red[w] : fmaxf(t, red[w]);
+      t = (norm == H2D_NORM_L2SQ) ? t + red[w] : fmax_nan(t, red[w]);
     *out = t;
     *counter = 0u;  // ready for the next call on this stream
   }

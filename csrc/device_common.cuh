@@ -1,6 +1,7 @@
 // Device-side building blocks shared by every heat2d kernel (sm_100a).
 #pragma once
 #include <cuda_runtime.h>
+#include <cmath>
 #include <cstdint>
 #include "heat2d.h"
 #include "host_common.h"
@@ -32,6 +33,7 @@ struct Geo {
   int32_t ax_lo, ax_hi, ay_lo, ay_hi;
   float a0, cx, cy;  // fp32 mode
   double dcx, dcy;   // strict modes
+  double dcx_s, dcy_s;   // dcx * 2^896, dcy * 2^896: the strict fast path works on operands scaled by 2^-896
 };
 
 inline Geo make_geo(const h2d_tile_t& t, const h2d_phys_t& p) {
@@ -46,6 +48,7 @@ inline Geo make_geo(const h2d_tile_t& t, const h2d_phys_t& p) {
   g.a0 = (float)(1.0 - 2.0 * p.cx - 2.0 * p.cy);
   g.cx = (float)p.cx; g.cy = (float)p.cy;
   g.dcx = p.cx; g.dcy = p.cy;
+  g.dcx_s = ldexp(p.cx, 896); g.dcy_s = ldexp(p.cy, 896);
   return g;
 }
 
@@ -119,9 +122,16 @@ __device__ __forceinline__ float warp_sum(float v) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
+// max that PROPAGATES NaN (fmaxf drops it): a diverged field must not report a small
+// finite LINF norm and be declared converged.  One FMNMX.NAN.
+__device__ __forceinline__ float fmax_nan(float a, float b) {
+  float r;
+  asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+}
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  for (int o = 16; o > 0; o >>= 1) v = fmax_nan(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
 }
 
@@ -143,14 +153,17 @@ __device__ __forceinline__ void st_relaxed_sys_f32(float* p, float v) {
 }
 
 // Spin until *flag >= want (wrap-safe) or the watchdog expires.  Returns false
-// on timeout.  One thread calls this; a dead peer must not hang the kernel
-// forever (failure detection).
+// on timeout, and at once when `fault` (optional) is already set: after one
+// peer has stalled, the remaining waits of this and of every queued launch
+// must not each burn the full timeout again.  One thread calls this; a dead
+// peer must not hang the kernel forever (failure detection).
 __device__ __forceinline__ bool wait_flag_ge(const uint32_t* flag, uint32_t want,
-                                             int64_t timeout_ns) {
+                                             int64_t timeout_ns, const uint32_t* fault = nullptr) {
   if ((int32_t)(ld_acquire_sys(flag) - want) >= 0) return true;
   const uint64_t t0 = globaltimer_ns();
   for (;;) {
     if ((int32_t)(ld_acquire_sys(flag) - want) >= 0) return true;
+    if (fault != nullptr && *reinterpret_cast<const volatile uint32_t*>(fault) != 0u) return false;
     if ((int64_t)(globaltimer_ns() - t0) > timeout_ns) return false;
     __nanosleep(64);
   }

@@ -165,11 +165,15 @@ double norm_dense(const float* a, const float* b, int64_t n, int norm, int threa
       acc += d * d;
     }
   } else {
-#pragma omp parallel for reduction(max : acc) num_threads(threads) if (threads > 1)
+    // NaN propagates (as in the CUDA kernels): a diverged field never looks converged
+    int has_nan = 0;
+#pragma omp parallel for reduction(max : acc) reduction(| : has_nan) num_threads(threads) if (threads > 1)
     for (int64_t i = 0; i < n; ++i) {
       double d = std::fabs((double)a[i] - (double)b[i]);
+      if (d != d) has_nan = 1;
       if (d > acc) acc = d;
     }
+    if (has_nan) acc = std::nan("");
   }
   return acc;
 }

@@ -45,9 +45,9 @@ __global__ void norm_finish_kernel(const float* local_val, float* const* vals,
   if (threadIdx.x == 0) failed = 0;
   __syncthreads();
   for (int r = threadIdx.x; r < world; r += blockDim.x) {
-    if (!wait_flag_ge(flags[rank] + par * world + r, seq, timeout_ns)) {
+    if (!wait_flag_ge(flags[rank] + par * world + r, seq, timeout_ns, fault)) {
       failed = 1;
-      if (fault) atomicExch(fault, 100u + r);
+      if (fault) atomicCAS(fault, 0u, 100u + r);   // keep the first cause
     }
   }
   __syncthreads();
@@ -56,7 +56,7 @@ __global__ void norm_finish_kernel(const float* local_val, float* const* vals,
     float t = 0.f;
     for (int r = 0; r < world; ++r) {
       const float x = *((volatile const float*)(mine + r));
-      t = (norm == H2D_NORM_L2SQ) ? t + x : fmaxf(t, x);
+      t = (norm == H2D_NORM_L2SQ) ? t + x : fmax_nan(t, x);
     }
     *out = t;
     if (!failed && t < eps) {

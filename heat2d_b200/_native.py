@@ -62,6 +62,8 @@ class PlanDesc(C.Structure):
         ("flags_in", C.c_void_p),
         ("scratch", C.c_void_p),
         ("spin_timeout_ns", C.c_int64),
+        ("layout", C.c_int32),
+        ("reserved", C.c_int32),
     ]
 
 
@@ -136,6 +138,12 @@ def cuda():
             lib.h2d_plan_run_dataflow.restype = C.c_int
             lib.h2d_plan_chunk_rows.argtypes = [P(Tile), C.c_int32, C.c_int32]
             lib.h2d_plan_chunk_rows.restype = C.c_int32
+            lib.h2d_plan_chunk_rows_ex.argtypes = [P(Tile), C.c_int32, C.c_int32, C.c_int32, C.c_int32]
+            lib.h2d_plan_chunk_rows_ex.restype = C.c_int32
+            lib.h2d_plan_strip_width.argtypes = [C.c_int32, C.c_int32]
+            lib.h2d_plan_strip_width.restype = C.c_int32
+            lib.h2d_plan_layout.argtypes = [vp]
+            lib.h2d_plan_layout.restype = C.c_int32
             lib.h2d_plan_create.argtypes = [P(PlanDesc)]
             lib.h2d_plan_create.restype = vp
             lib.h2d_plan_destroy.argtypes = [vp]

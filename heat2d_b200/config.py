@@ -16,6 +16,7 @@ from ._native import ARITH, BOUNDARY, INIT, KMAX, NORM
 BACKENDS = ("fused", "single", "plain", "nccl-halo", "resident", "cpu")
 DUMPS = ("none", "prtdat", "rowmajor", "binary")
 CONV_MODES = ("exact", "fused-k")
+LAYOUTS = {"auto": 0, "v4": 1, "ab2": 2, "ab4": 3}
 
 
 class ConfigError(ValueError):
@@ -57,6 +58,8 @@ class HeatConfig:
     spin_timeout_s: float = 10.0
     dataflow: bool = False       # one dataflow launch per run of equal-k sweeps
                                  # (single tile, no convergence test; h2d_plan_run_dataflow)
+    layout: str = "auto"         # lane layout of the fp32 kernels: auto | v4 | ab2 | ab4 (csrc/tk_task.cuh);
+                                 # same bits, different speed; strict arithmetic always runs v4
 
     def validate(self, world_size: Optional[int] = None) -> "HeatConfig":
         if self.nx < 1 or self.ny < 1:
@@ -86,6 +89,8 @@ class HeatConfig:
                 raise ConfigError(f"dump must be a comma list of {DUMPS}")
         if self.conv_mode not in CONV_MODES:
             raise ConfigError(f"conv_mode must be one of {CONV_MODES}")
+        if self.layout not in LAYOUTS:
+            raise ConfigError(f"layout must be one of {sorted(LAYOUTS)}")
         if not 1 <= self.k <= KMAX:
             raise ConfigError(f"k must be in [1, {KMAX}]")
         if self.halo < self.k:

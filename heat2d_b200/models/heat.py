@@ -37,6 +37,12 @@ def padded_geometry(spec: TileSpec, nx: int, ny: int, halo: int) -> N.Tile:
     return N.Tile(nx, ny, spec.x0, spec.y0, spec.rows, spec.cols, halo, halo_c, pitch)
 
 
+def _layout_code(cfg: HeatConfig) -> int:
+    """h2d_plan_desc_t::layout for a configuration (the dataflow launch exists for v4 only)."""
+    from ..config import LAYOUTS
+    return LAYOUTS["v4"] if (cfg.dataflow and cfg.layout == "auto") else LAYOUTS[cfg.layout]
+
+
 def padded_bytes(tile: N.Tile) -> int:
     return (tile.rows + 2 * tile.halo_r) * tile.pitch * 4
 
@@ -126,7 +132,7 @@ class TileEngine:
 
     def __init__(self, field: TileField, phys: N.Phys, kmax: int, chunk_rows: int, world: int,
                  rank: int, flags_in: torch.Tensor, vals: torch.Tensor, nflags: torch.Tensor,
-                 spin_timeout_s: float = 10.0):
+                 spin_timeout_s: float = 10.0, layout: int = 0):
         self.field = field
         self.phys = phys
         self.kmax = kmax
@@ -134,6 +140,7 @@ class TileEngine:
         self.world, self.rank = world, rank
         self.flags_in, self.vals, self.nflags = flags_in, vals, nflags
         self.spin_timeout_s = spin_timeout_s
+        self.layout = layout
         dev = field.device
         self.norm_total = torch.zeros(1, dtype=torch.float32, device=dev)
         # run-control word: 0 = iterating, q = check number q stopped the run
@@ -147,7 +154,7 @@ class TileEngine:
         f = self.field
         self.plan = K.Plan(f.tile, self.phys, f.buf[0].data_ptr(), f.buf[1].data_ptr(), self.kmax,
                            self.chunk_rows, peers=peers, flags_in_ptr=self.flags_in.data_ptr(),
-                           spin_timeout_s=self.spin_timeout_s, device=f.device)
+                           spin_timeout_s=self.spin_timeout_s, device=f.device, layout=self.layout)
         self.vals_ptrs = torch.tensor(all_vals_ptrs, dtype=torch.int64, device=f.device)
         self.flags_ptrs = torch.tensor(all_nflags_ptrs, dtype=torch.int64, device=f.device)
         self._fault = tensor_from_ptr(self.plan.fault_ptr, (1,), torch.int32, f.device)
@@ -236,7 +243,7 @@ class Heat2DSolver:
             vals = torch.zeros(2 * w, dtype=torch.float32, device=dev)
             nflags = torch.zeros(2 * w, dtype=torch.int32, device=dev)
             self.engines.append(TileEngine(f, self.phys, max(cfg.k, 1), cfg.chunk_rows, w, r, flags_in,
-                                           vals, nflags, cfg.spin_timeout_s))
+                                           vals, nflags, cfg.spin_timeout_s, _layout_code(cfg)))
         all_vals = [e.vals.data_ptr() for e in self.engines]
         all_nfl = [e.nflags.data_ptr() for e in self.engines]
         for r, e in enumerate(self.engines):

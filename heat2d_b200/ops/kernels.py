@@ -164,7 +164,7 @@ class Plan:
 
     def __init__(self, tile: N.Tile, phys: N.Phys, buf0_ptr: int, buf1_ptr: int, kmax: int,
                  chunk_rows: int = 0, peers: Optional[dict] = None, flags_in_ptr: int = 0,
-                 scratch_ptr: int = 0, spin_timeout_s: float = 10.0, device=None):
+                 scratch_ptr: int = 0, spin_timeout_s: float = 10.0, device=None, layout: int = 0):
         self._lib = N.cuda()
         self.tile, self.phys, self.kmax = tile, phys, kmax
         self.device = device
@@ -187,6 +187,7 @@ class Plan:
         d.flags_in = flags_in_ptr or None
         d.scratch = scratch_ptr or None
         d.spin_timeout_ns = int(spin_timeout_s * 1e9)
+        d.layout = int(layout)
         self._desc = d
         with torch.cuda.device(device):
             h = self._lib.h2d_plan_create(C.byref(d))
@@ -303,6 +304,11 @@ class Plan:
         return int(self._lib.h2d_plan_launch_count(self._h))
 
     @property
+    def layout(self) -> str:
+        """Lane layout the plan's kernels use: 'v4', 'ab2' or 'ab4'."""
+        return {1: "v4", 2: "ab2", 3: "ab4"}.get(int(self._lib.h2d_plan_layout(self._h)), "?")
+
+    @property
     def norm_ptr(self) -> int:
         return int(self._lib.h2d_plan_norm_ptr(self._h))
 
@@ -324,19 +330,3 @@ class Plan:
             self.close()
         except Exception:
             pass
-
-
-class DevWord:
-    """A torch view of a 4-byte device word at a raw address (read-back helper)."""
-
-    def __init__(self, ptr: int, dtype, device):
-        self.ptr = ptr
-        self.dtype = dtype
-        self.device = device
-        self.__cuda_array_interface__ = {
-            "shape": (1,), "typestr": "<f4" if dtype == torch.float32 else "<i4",
-            "data": (ptr, False), "version": 2, "strides": None,
-        }
-
-    def tensor(self) -> torch.Tensor:
-        return torch.as_tensor(self, device=self.device)

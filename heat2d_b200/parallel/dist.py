@@ -31,7 +31,7 @@ import torch.distributed as dist
 
 from .. import _native as N
 from ..config import HeatConfig
-from ..models.heat import (Heat2DSolver, RunResult, TileEngine, TileField, padded_bytes,
+from ..models.heat import (Heat2DSolver, RunResult, TileEngine, TileField, _layout_code, padded_bytes,
                            padded_geometry, tensor_from_ptr)
 from ..ops import kernels as K
 from .decomp import DIRS, Decomposition, OPPOSITE
@@ -141,7 +141,7 @@ class DistributedHeat2DSolver(Heat2DSolver):
         vals = tensor_from_ptr(a.ptr + a.off_vals, (2 * w,), torch.float32, dev, owner=a)
         nflags = tensor_from_ptr(a.ptr + a.off_nflags, (2 * w,), torch.int32, dev, owner=a)
         eng = TileEngine(f, self.phys, cfg.k, cfg.chunk_rows, w, r, flags_in, vals, nflags,
-                         cfg.spin_timeout_s)
+                         cfg.spin_timeout_s, _layout_code(cfg))
         self.engines = [eng]
 
         # exchange handles + geometry (start-up only)

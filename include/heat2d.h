@@ -188,12 +188,25 @@ typedef struct h2d_plan_desc {
   /* convergence scratch (optional): >= h2d_plan_scratch_bytes() bytes          */
   void* scratch;
   int64_t spin_timeout_ns;  /* watchdog for flag waits; 0 = 10 s                  */
+  /* Lane layout of the fp32 kernels (csrc/tk_task.cuh): 0 = library default
+   * (H2D_FP32_LAYOUT=v4|ab2|ab4 overrides it), 1 = v4 (4 adjacent columns per lane,
+   * 128-column strips), 2 = ab2 / 3 = ab4 (two half-strips packed in f32x2, 128- /
+   * 256-column strips).  Strict arithmetic always uses v4.  Results are bit-identical. */
+  int32_t layout;
+  int32_t reserved;
 } h2d_plan_desc_t;
 
 size_t h2d_plan_scratch_bytes(const h2d_tile_t* tile, int32_t kmax, int32_t chunk_rows);
 /* Rows per streaming task the plan would choose for this tile (pure host computation:
  * the makespan model of DESIGN.md section 3; with_peers != 0 asks for >= 4 waves). */
 int32_t h2d_plan_chunk_rows(const h2d_tile_t* tile, int32_t kmax, int32_t with_peers);
+/* The same for a given arithmetic (H2D_ARITH_*) and lane layout (0 = default), and the
+ * strip width in columns that combination works with (128 or 256). */
+int32_t h2d_plan_chunk_rows_ex(const h2d_tile_t* tile, int32_t kmax, int32_t with_peers, int32_t arith,
+                               int32_t layout);
+int32_t h2d_plan_strip_width(int32_t arith, int32_t layout);
+/* Lane layout a plan was built with (1 = v4, 2 = ab2, 3 = ab4). */
+int32_t h2d_plan_layout(const h2d_plan_t* plan);
 h2d_plan_t* h2d_plan_create(const h2d_plan_desc_t* desc);
 void h2d_plan_destroy(h2d_plan_t* plan);
 

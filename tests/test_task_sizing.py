@@ -7,10 +7,12 @@ import pytest
 from heat2d_b200 import _native as N
 
 
-def chunk_rows(rows, cols, k=8, peers=False):
+def chunk_rows(rows, cols, k=8, peers=False, layout=1):
+    """layout 1 = v4 (128-column strips, 12 / 16 resident warps): the sweeps these numbers were
+    fitted to; layout 3 = ab4 (256-column strips, 8 warps)."""
     lib = N.cuda()
     t = N.make_tile(rows, cols, 0, 0, rows, cols, 8, 32, (cols + 64 + 31) // 32 * 32)
-    return lib.h2d_plan_chunk_rows(C.byref(t), k, int(peers))
+    return lib.h2d_plan_chunk_rows_ex(C.byref(t), k, int(peers), 0, layout)
 
 
 def waves(rows, cols, R, k=8):
@@ -41,3 +43,13 @@ def test_plans_with_peers_keep_edge_tasks_short():
         R = chunk_rows(rows, cols, peers=True)
         assert waves(rows, cols, R) > 3.0
         assert R <= chunk_rows(rows, cols, peers=False)
+
+
+def test_wide_strip_layout_fills_whole_waves_too():
+    # ab4: 256-column strips (240 stored at k = 8), 8 resident warps per SM
+    R = chunk_rows(32768, 32768, layout=3)
+    ns = -(-32768 // 240)
+    w = -(-32768 // R) * ns / (148 * 8)
+    assert 200 <= R <= 2048 and (w <= round(w) + 1e-9 or w - int(w) > 0.85), (R, w)
+    assert N.cuda().h2d_plan_strip_width(0, 3) == 256 and N.cuda().h2d_plan_strip_width(0, 1) == 128
+    assert N.cuda().h2d_plan_strip_width(2, 3) == 128     # strict arithmetic always runs v4

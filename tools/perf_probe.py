@@ -35,6 +35,8 @@ def main():
     ap.add_argument("--chunks", default="0")
     ap.add_argument("--arith", default="fp32")
     ap.add_argument("--plain", action="store_true")
+    ap.add_argument("--layouts", default="auto", help="comma list of auto,v4,ab2,ab4 (fp32 only)")
+    ap.add_argument("--tag", default="")
     a = ap.parse_args()
     nx, ny = (a.nx or a.n), (a.ny or a.n)
     out = []
@@ -42,13 +44,15 @@ def main():
         g = time_cfg(HeatConfig(nx=nx, ny=ny, steps=16, backend="plain", k=1, arith=a.arith))
         out.append({"kernel": "plain_k1", "glups": g})
         print(out[-1], flush=True)
-    for k in map(int, a.ks.split(",")):
-        for ch in map(int, a.chunks.split(",")):
-            g = time_cfg(HeatConfig(nx=nx, ny=ny, steps=a.steps, k=k, chunk_rows=ch, arith=a.arith))
-            out.append({"kernel": f"tk_k{k}", "chunk_rows": ch, "arith": a.arith, "n": [nx, ny], "glups": g})
-            print(out[-1], flush=True)
+    for lay in a.layouts.split(","):
+        for k in map(int, a.ks.split(",")):
+            for ch in map(int, a.chunks.split(",")):
+                g = time_cfg(HeatConfig(nx=nx, ny=ny, steps=a.steps, k=k, chunk_rows=ch, arith=a.arith, layout=lay))
+                out.append({"kernel": f"tk_k{k}", "layout": lay, "chunk_rows": ch, "arith": a.arith, "n": [nx, ny],
+                            "steps": a.steps, "strict_fast": os.environ.get("H2D_STRICT_FAST", "1"), "glups": g})
+                print(out[-1], flush=True)
     os.makedirs("gpurun_out", exist_ok=True)
-    with open(f"gpurun_out/probe_{a.arith}_{nx}x{ny}.json", "w") as f:
+    with open(f"gpurun_out/probe_{a.arith}_{nx}x{ny}{a.tag}.json", "w") as f:
         json.dump(out, f, indent=1)
 
 
