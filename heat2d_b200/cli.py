@@ -181,18 +181,38 @@ def main(argv=None) -> int:
         if not dumps:
             return
         os.makedirs(cfg.out_dir, exist_ok=True)
-        field = solver.gather(as_numpy=True) if cfg.backend == "cpu" else solver.gather()
-        if rank != 0:
+        bin_path = os.path.join(cfg.out_dir, f"{stem}_binary.dat")
+        txt_path = os.path.join(cfg.out_dir, f"{stem}.dat")
+        if world > 1:
+            # Every rank writes its own tile straight into the shared file at its place in the
+            # nx x ny array — the MPI-IO subarray view of grad1612_mpi_heat.c:178-190,283-285 —
+            # and rank 0 then converts the binary file to text exactly as the reference does
+            # (:191-203,286-298).  Nothing is gathered: at 32768^2 a gather would funnel 4 GiB
+            # through one rank and one PCIe link.
+            import torch.distributed as dist
+            keep = "binary" in dumps
+            path = bin_path if keep else os.path.join(cfg.out_dir, f".{stem}_binary.tmp")
+            if rank == 0:
+                open(path, "ab").close()     # create without truncating (the reference opens WRONLY|CREATE)
+            dist.barrier()
+            for x0, y0, tile in solver.local_tiles():
+                D.write_binary_tile(path, tile, cfg.nx, cfg.ny, x0, y0, truncate=False)
+            dist.barrier()
+            if rank == 0:
+                for dname in dumps:
+                    if dname in ("prtdat", "rowmajor"):
+                        D.binary_to_text(path, txt_path, cfg.nx, cfg.ny, dname)
+                if not keep:
+                    os.remove(path)
             return
+        field = solver.gather(as_numpy=True) if cfg.backend == "cpu" else solver.gather()
         for dname in dumps:
-            if rank == 0 and stem == "initial" and style != "grad1612_cuda":
-                pass
             if dname == "binary":
-                D.write_binary(os.path.join(cfg.out_dir, f"{stem}_binary.dat"), field, truncate=False)
+                D.write_binary(bin_path, field, truncate=False)
             elif dname == "prtdat":
-                D.write_prtdat(os.path.join(cfg.out_dir, f"{stem}.dat"), field)
+                D.write_prtdat(txt_path, field)
             else:
-                D.write_rowmajor(os.path.join(cfg.out_dir, f"{stem}.dat"), field)
+                D.write_rowmajor(txt_path, field)
 
     if rank == 0 and dumps:
         print("Writing initial.dat ..." if style != "mpi_heat2Dn"

@@ -517,6 +517,13 @@ class Heat2DSolver:
         torch.cuda.synchronize(self.device)
         return out
 
+    def local_tiles(self):
+        """[(x0, y0, host ndarray)] of the tiles this process owns (the per-rank dump)."""
+        out = []
+        for f in self.fields:
+            out.append((f.tile.x0, f.tile.y0, f.owned(self.parity).cpu().numpy()))
+        return out
+
     def owned_views(self) -> List[torch.Tensor]:
         return [f.owned(self.parity) for f in self.fields]
 

@@ -512,5 +512,10 @@ class HaloExchangeSolver:
         dist.send(mine, dst=dst)
         return None
 
+    def local_tiles(self):
+        """[(x0, y0, host ndarray)] of the tile this rank owns (the per-rank dump)."""
+        t = self.field.tile
+        return [(t.x0, t.y0, self.field.owned(self.parity).cpu().numpy())]
+
     def close(self):
         pass

@@ -51,8 +51,8 @@ def test_dataflow_matches_the_oracle(arith):
     nx, ny = 200, 300
     u0 = rand_grid(nx, ny, 5)
     got, res = run(u0, True, steps=8 * 4 + 3, k=8, chunk_rows=24, arith=arith)
-    # 4 sweeps of 8 in one dataflow launch + one ordinary launch of 3
-    assert res.launches == 2
+    # 35 steps at k = 8: five sweeps of 7 (balanced schedule), all in one dataflow launch
+    assert res.launches == 1
     want = u0.copy()
     K.cpu_run(want, 35, N.make_phys(0.1, 0.1, "fixed", arith))
     assert np.array_equal(got, want)
