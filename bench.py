@@ -346,7 +346,7 @@ def main(argv=None):
         px, py = d.px, d.py
     nx, ny = (n * px, n * py) if a.weak else (n, n)
     backend = "nccl-halo" if a.impl == "nccl-halo" else "fused"
-    k = 1 if backend == "nccl-halo" else a.k
+    k = a.k   # nccl-halo: --k 8 = same kernel + grouped NCCL exchange of 8-wide bands; --k 1 = one cell per step
     cfg = HeatConfig(nx=nx, ny=ny, steps=a.steps, px=px, py=py, k=k, halo=max(k, 8), arith=a.arith,
                      boundary="fixed", init="exact", backend=backend, chunk_rows=a.chunk_rows,
                      conv=a.conv, interval=20, eps=0.0 if a.conv else 0.1, conv_mode="exact")

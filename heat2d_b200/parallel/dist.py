@@ -316,7 +316,7 @@ class HaloExchangeSolver:
         self.decomp = Decomposition(cfg.nx, cfg.ny, cfg.px, cfg.py, cfg.uneven)
         self.spec = self.decomp.tile(self.rank)
         self.phys = N.make_phys(cfg.cx_eff, cfg.cy_eff, cfg.boundary, cfg.arith)
-        self.field = TileField(self.spec, cfg.nx, cfg.ny, max(cfg.halo, 1), self.device)
+        self.field = TileField(self.spec, cfg.nx, cfg.ny, max(cfg.halo, cfg.k, 1), self.device)
         self.parity = 0
         self.steps_done = cfg.start_step
         t = self.field.tile
@@ -324,6 +324,18 @@ class HaloExchangeSolver:
                       for d in "NSWE"}
         self._recv = {d: torch.empty_like(self._send[d]) for d in "NSWE"}
         self.kernel_launches = 0
+        # k > 1 (GPU only): the SAME temporal-blocked kernel as the fused product, without peers,
+        # fed by one grouped NCCL exchange of k-wide bands per launch — the comparison that
+        # isolates the halo mechanism (peer stores + flags vs pack / send / recv / unpack)
+        self.plan = None
+        if cfg.k > 1:
+            if not self.on_gpu:
+                raise ValueError("the nccl-halo baseline runs k > 1 on GPUs only (CPU / gloo: k = 1)")
+            if cfg.conv:
+                raise ValueError("the nccl-halo baseline checks convergence with k = 1 only")
+            f = self.field
+            self.plan = K.Plan(f.tile, self.phys, f.buf[0].data_ptr(), f.buf[1].data_ptr(), cfg.k,
+                               cfg.chunk_rows, device=self.device, layout=_layout_code(cfg))
 
     def initialize(self, mode: Optional[str] = None):
         mode = mode or self.cfg.init
@@ -428,6 +440,50 @@ class HaloExchangeSolver:
         self._sub_step(1, t.rows - 1, 0, 1)                     # ... and edge columns
         self._sub_step(1, t.rows - 1, t.cols - 1, t.cols)
 
+    def _exchange_bands(self, w: int):
+        """k-wide halo exchange in two grouped rounds: W/E column bands first, then N/S row bands
+        INCLUDING the ghost columns just received, which carries the corners along (temporal
+        blocking needs them; the reference, one cell per step, never did: grad1612_mpi_heat.c:140-144)."""
+        f, t = self.field, self.field.tile
+        src = f.buf[self.parity]
+        hr, hc, R, Cn = t.halo_r, t.halo_c, t.rows, t.cols
+        nbs = self.spec.neighbours
+        for phase in ("WE", "NS"):
+            ops, pending = [], []
+            for d in phase:
+                if nbs[d] is None:
+                    continue
+                if d == "W":
+                    out, dst = src[hr:hr + R, hc:hc + w], src[hr:hr + R, hc - w:hc]
+                elif d == "E":
+                    out, dst = src[hr:hr + R, hc + Cn - w:hc + Cn], src[hr:hr + R, hc + Cn:hc + Cn + w]
+                elif d == "N":
+                    out, dst = src[hr:hr + w, hc - w:hc + Cn + w], src[hr - w:hr, hc - w:hc + Cn + w]
+                else:
+                    out, dst = src[hr + R - w:hr + R, hc - w:hc + Cn + w], src[hr + R:hr + R + w, hc - w:hc + Cn + w]
+                sbuf = out.contiguous()
+                rbuf = torch.empty_like(sbuf)
+                ops.append(dist.P2POp(dist.isend, sbuf, nbs[d]))
+                ops.append(dist.P2POp(dist.irecv, rbuf, nbs[d]))
+                pending.append((dst, rbuf))
+            if ops:
+                for wk in dist.batch_isend_irecv(ops):
+                    wk.wait()
+            for dst, rbuf in pending:
+                dst.copy_(rbuf)
+
+    def _run_blocked(self, steps: int):
+        """k steps per exchange: grouped NCCL exchange of k-wide bands, then one launch of the
+        peer-less temporal-blocked kernel."""
+        from ..config import make_schedule
+        for L in make_schedule(steps, self.cfg.k, False, 20, "exact", self.steps_done):
+            if self.world > 1:
+                self._exchange_bands(L.k)
+            self.plan.launch(self.parity, L.k, 0, "none")
+            self.kernel_launches += 1
+            self.parity ^= 1
+            self.steps_done += L.k
+
     def _step(self):
         f = self.field
         if self.on_gpu:
@@ -462,6 +518,9 @@ class HaloExchangeSolver:
         t0 = time.perf_counter()
         converged, last, checks, iterations = False, float("nan"), 0, None
         done0 = self.steps_done
+        if self.plan is not None:
+            self._run_blocked(steps)
+            steps = 0
         for s in range(self.steps_done, self.steps_done + steps):
             t_ = self.field.tile
             if self.world > 1 and not self.on_gpu and t_.rows >= 3 and t_.cols >= 3:
@@ -518,4 +577,6 @@ class HaloExchangeSolver:
         return [(t.x0, t.y0, self.field.owned(self.parity).cpu().numpy())]
 
     def close(self):
-        pass
+        if self.plan is not None:
+            self.plan.close()
+            self.plan = None

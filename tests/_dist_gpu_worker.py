@@ -25,6 +25,8 @@ def main():
         s = cls(cfg, device)
         if case.get("random"):
             u0 = (np.random.default_rng(7).random((cfg.nx, cfg.ny), dtype=np.float32) * 1e4).astype(np.float32)
+            if case.get("negative"):
+                u0[cfg.nx // 3:cfg.nx // 2, :] *= np.float32(-1.0)   # the strict fast path must fall back there
             s.load(u0)
         else:
             u0 = K.cpu_initial_grid(cfg.nx, cfg.ny, cfg.init)

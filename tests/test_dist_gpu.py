@@ -51,6 +51,11 @@ def _cases(px, py):
         {"name": "fused-conv", "cfg": dict(nx=48, ny=64, px=px, py=py, k=8, steps=100000, backend="fused",
                                            boundary="ghost-ring", conv=True, interval=20, eps=0.1)},
         {"name": "nccl-halo", "random": True, "cfg": dict(base, steps=9, backend="nccl-halo", k=1)},
+        # the fair baseline: same temporal-blocked kernel, k-wide bands over NCCL once per launch
+        {"name": "nccl-halo-k8", "random": True, "cfg": dict(base, steps=43, backend="nccl-halo", k=8)},
+        {"name": "fused-k8-ab4", "random": True, "cfg": dict(base, steps=41, backend="fused", layout="ab4")},
+        {"name": "fused-strict-fma-mixed-sign", "random": True, "negative": True,
+         "cfg": dict(base, steps=24, backend="fused", arith="strict-fma")},
     ]
 
 
@@ -88,9 +93,6 @@ def test_flag_protocol_under_injected_delays():
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
-@pytest.mark.skipif(os.environ.get("H2D_EXPERIMENTAL") != "1",
-                    reason="validated on one GPU with virtual tiles (test_gpu_kernels.py); the one-process-per-GPU "
-                           "form has not run on multi-GPU hardware yet: set H2D_EXPERIMENTAL=1")
 @pytest.mark.parametrize("delay", [False, True])
 def test_pipelined_solve_on_column_strips(delay):
     """End to end on a 1 x P grid: upload / window launches with W-E halo exchange / download,
@@ -101,6 +103,10 @@ def test_pipelined_solve_on_column_strips(delay):
          "cfg": dict(nx=3000, ny=256 * n, px=1, py=n, k=8, steps=83, backend="fused", chunk_rows=64)},
         {"name": "pipelined-k5-ring", "random": True, "pipelined": True,
          "cfg": dict(nx=1500, ny=192 * n, px=1, py=n, k=5, steps=41, backend="fused", boundary="ghost-ring")},
+        # the last strip owns 4 columns (cols = 2 * 112 + 4): the strip before it depends on the E
+        # ghost columns and must take part in the flag protocol as well
+        {"name": "pipelined-k8-narrow-last-strip", "random": True, "pipelined": True,
+         "cfg": dict(nx=2000, ny=228 * n, px=1, py=n, k=8, steps=50, backend="fused", chunk_rows=48, layout="v4")},
     ]
     out = _run(n, {"cases": cases}, env_extra={"H2D_DEBUG_DELAY": "1"} if delay else None)
     assert out["ok"], out

@@ -348,7 +348,10 @@ def test_solve_api_uses_the_pipelined_path_for_pinned_input():
 
 
 @pytest.mark.parametrize("py,shape,steps,k,block", [(2, (1500, 512), 83, 8, 0), (3, (900, 768), 41, 5, 128),
-                                                    (4, (2200, 1024), 24, 8, 256)])
+                                                    (4, (2200, 1024), 24, 8, 256),
+                                                    # 228 columns per tile: the last task strip owns 4 < k
+                                                    # columns, the strip before it reads the E ghosts too
+                                                    (2, (1200, 456), 50, 8, 0)])
 def test_pipelined_solve_on_virtual_column_strips(py, shape, steps, k, block):
     """1 x P tiles in one process: upload / window launches with W-E halo exchange / download,
     then an ordinary run() from the state it left (flags, epochs, ghost margins)."""
@@ -356,7 +359,7 @@ def test_pipelined_solve_on_virtual_column_strips(py, shape, steps, k, block):
     u0 = rand_grid(nx, ny, py)
     hin = torch.from_numpy(u0).pin_memory()
     hout = torch.empty((nx, ny), dtype=torch.float32).pin_memory()
-    s = Heat2DSolver(HeatConfig(nx=nx, ny=ny, steps=steps, k=k, px=1, py=py, chunk_rows=48), DEV)
+    s = Heat2DSolver(HeatConfig(nx=nx, ny=ny, steps=steps, k=k, px=1, py=py, chunk_rows=48, layout="v4"), DEV)
     res = s.solve_pipelined(hin, hout, block_rows=block)
     torch.cuda.synchronize()
     assert res.steps_done == steps
