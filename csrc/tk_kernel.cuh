@@ -21,19 +21,6 @@ struct TkBounds {
   static constexpr int min_blocks = LAY == LAY_AB4 ? ((K <= 4) ? 3 : 2) : ((K <= 5) ? 4 : 3);
 };
 
-// The generic strict evaluation (plain F2F conversions), out of line: taken when the data
-// of a task is outside the fast path's domain, or when the previous launch said most is.
-template <int K, int ARITH, bool XTR>
-__device__ __noinline__ float strict_slow_task(const CUtensorMap* tmap, const TkArgs& a, int strip, int chunk,
-                                               bool comm_edge, uint32_t ring, uint32_t bars, uint32_t we_stage,
-                                               int lane, uint32_t* track) {
-  uint32_t t = 0u;
-  const float acc = run_task_v4<K, ARITH, false, true, XTR ? XM_COMM : XM_NONE, false>(
-      tmap, a, a.dst, strip, chunk, comm_edge, ring, bars, we_stage, lane, t);
-  *track = t;
-  return acc;
-}
-
 // XTR = false: a launch with neither peers nor a convergence norm (the common single-GPU
 // launch): the kernel contains no forwarding / reduction code at all, so that code cannot
 // cost the hot loop registers.
@@ -144,14 +131,13 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
         const unsigned prev = *reinterpret_cast<const volatile unsigned*>(a.strict_fb + (a.seq + 2u) % 3u);
         if ((int64_t)prev * 4 > (int64_t)a.n_tasks) fast = false;
       }
-      bool done = false;
-      if constexpr (STRICT) {
-        if (!fast) {
-          acc = strict_slow_task<K, ARITH, XTR>(&tmap, a, strip, chunk, comm_edge, ring, bars, we_stage, lane, &track);
-          done = true;
-        }
-      }
-      if (done) {
+      // Strict modes: try the fast evaluation unless the previous launch said most tasks are
+      // outside its domain; a task whose data is (negative, non-finite or huge anywhere in its
+      // pipeline) is REDONE with the plain evaluation below — it overwrites every store, local
+      // and remote, before the epoch is published.
+      bool need_slow = STRICT && !fast;
+      int box0 = 0;
+      if (need_slow) {
       } else if (XTR && comm_edge && frozen) {
         acc = run_task<K, ARITH, LAY, IMM, true, XC, STRICT>(&tmap, a, a.dst, strip, chunk, true, ring, bars, we_stage, lane, track);
       } else if (XTR && comm_edge) {
@@ -166,22 +152,19 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
         acc = run_task<K, ARITH, LAY, IMM, false, XM_NONE, STRICT>(&tmap, a, a.dst, strip, chunk, false, ring, bars, we_stage, lane, track);
       }
       if constexpr (STRICT) {
-        // A negative, non-finite or huge value anywhere in the task's pipeline: the fast
-        // evaluation is not valid for it.  Redo the whole task with the plain one (it
-        // overwrites every store, local and remote, before the epoch is published).
-        const bool bad = __any_sync(0xffffffffu, track >= STRICT_FAST_LIMIT);
-        if (bad) {
-          if (lane == 0) atomicAdd(a.strict_fb + a.seq % 3u, 1u);
-          if (fast) {
-            __syncwarp();
-            if (lane == 0) {
-#pragma unroll
-              for (int s = 0; s < TK_STAGES; ++s) { mbar_inval(bars + s * 8); mbar_init(bars + s * 8, 1); }
-              asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-            }
-            __syncwarp();
-            acc = strict_slow_task<K, ARITH, XTR>(&tmap, a, strip, chunk, comm_edge, ring, bars, we_stage, lane, &track);
-          }
+        if (!need_slow && __any_sync(0xffffffffu, track >= STRICT_FAST_LIMIT)) {
+          need_slow = true;
+          // the ring's mbarriers have completed one phase per box: the second run continues there
+          box0 = (r_hi - r_lo + 2 * K + TK_BR - 1) / TK_BR;
+          __syncwarp();
+        }
+        if (need_slow) {
+          // one generic instantiation (boundary selects and extras always compiled in): rare path
+          acc = run_task_v4<K, ARITH, false, true, XC, false>(&tmap, a, a.dst, strip, chunk, comm_edge, ring, bars,
+                                                              we_stage, lane, track, box0);
+          // feeds the next launch's decision, whichever way this task got here
+          const bool bad = __any_sync(0xffffffffu, track >= STRICT_FAST_LIMIT);
+          if (bad && lane == 0) atomicAdd(a.strict_fb + a.seq % 3u, 1u);
         }
       }
 

@@ -304,8 +304,16 @@ __device__ __forceinline__ void setup_out(OutCtx<NSEG>& oc, const TkArgs& a, boo
 constexpr uint32_t STRICT_FAST_LIMIT = 0x7f000000u;
 
 __device__ __forceinline__ double up_scaled(float f) {
+  // (hi, lo) = (b >> 3, b << 29) is the 64-bit product b * 2^29: ONE IMAD.WIDE instead of two
+  // shifts — the kernel is bound by instruction issue, not by a pipe
+#ifndef H2D_STRICT_SHIFT_PAIR
+  unsigned long long v;
+  asm("mul.wide.u32 %0, %1, 0x20000000;" : "=l"(v) : "r"(__float_as_uint(f)));
+  return __longlong_as_double((long long)v);
+#else
   const uint32_t b = __float_as_uint(f);
   return __hiloint2double((int)(b >> 3), (int)(b << 29));
+#endif
 }
 
 template <int ARITH>
@@ -354,7 +362,11 @@ __device__ __forceinline__ uint32_t umax4(uint32_t t, const float4& v) {
 template <int K, int ARITH, bool IMM, bool FROZEN, int XM, bool FAST>
 __device__ __forceinline__ float run_task_v4(const CUtensorMap* tmap, const TkArgs& a, float* dst_base,
                                              int strip, int chunk, bool comm_edge, uint32_t ring,
-                                             uint32_t bars, uint32_t we_stage, int lane, uint32_t& track) {
+                                             uint32_t bars, uint32_t we_stage, int lane, uint32_t& track,
+                                             int box0 = 0) {
+  // box0: boxes this warp's ring has already carried in this kernel (a task that is run a
+  // second time continues the stage / phase sequence of its mbarriers instead of
+  // re-initialising them)
   constexpr bool EXTRAS = XM != XM_NONE;   // accumulates the norm (when the launch has one)
   constexpr bool COMM = XM == XM_COMM;     // forwards to neighbours
   constexpr bool TRACK = ARITH != H2D_ARITH_FP32;
@@ -408,7 +420,7 @@ __device__ __forceinline__ float run_task_v4(const CUtensorMap* tmap, const TkAr
   }
 
   auto issue = [&](int b) {
-    const int s = b % TK_STAGES;
+    const int s = (box0 + b) % TK_STAGES;
     const uint32_t bar = bars + s * 8;
     mbar_expect_tx(bar, STAGE_BYTES);
     tma_load_2d(ring + s * STAGE_BYTES, tmap, tc0, tc1 + b * TK_BR, bar);
@@ -517,8 +529,8 @@ __device__ __forceinline__ float run_task_v4(const CUtensorMap* tmap, const TkAr
   auto boxes = [&](auto Ftag, int b_lo, int b_hi) {
 #pragma unroll 1
     for (int b = b_lo; b < b_hi; ++b) {
-      const int s = b % TK_STAGES;
-      mbar_wait(bars + s * 8, (uint32_t)((b / TK_STAGES) & 1));
+      const int s = (box0 + b) % TK_STAGES;
+      mbar_wait(bars + s * 8, (uint32_t)(((box0 + b) / TK_STAGES) & 1));
       const uint32_t sbase = ring + s * STAGE_BYTES + lane * 16;
 #pragma unroll 1
       for (int rr = 0; rr < TK_BR; rr += 3) {

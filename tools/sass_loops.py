@@ -11,6 +11,8 @@ import sys
 
 
 def main():
+    import signal
+    signal.signal(signal.SIGPIPE, signal.SIG_DFL)
     src = sys.stdin if len(sys.argv) < 2 or not sys.argv[-1].endswith(".sass") else open(sys.argv[-1])
     min_n = next((int(a) for a in sys.argv[1:] if a.isdigit()), 200)
     rows = []
