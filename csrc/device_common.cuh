@@ -102,21 +102,11 @@ __device__ __forceinline__ float4 point4(const float4& u, const float4& c, const
     const float2 ns23 = make_float2(__fadd_rn(c.w, c.y), __fadd_rn(R, c.z));
     const float2 g01 = __ffma2_rn(cy, ns01, __fmul2_rn(a0, make_float2(c.x, c.y)));
     const float2 g23 = __ffma2_rn(cy, ns23, __fmul2_rn(a0, make_float2(c.z, c.w)));
-#ifndef H2D_V4_MIX
-#define H2D_V4_MIX 0
-#endif
-    // H2D_V4_MIX (experiment): how many of the two vertical sums are issued as scalar pairs
-    // instead of one packed instruction — same bits, different split between the pipes.
-#if H2D_V4_MIX >= 1
-    const float2 ew01 = make_float2(__fadd_rn(d.x, u.x), __fadd_rn(d.y, u.y));
-#else
+    // (Issuing one or both vertical sums as scalar pairs, to move work from the packed to the
+    // scalar fp32 pipe, was measured SLOWER on B200: 4234 / 4182 vs 4465 GLUP/s at 32768^2 —
+    // the kernel is bound by instruction issue as much as by the packed pipe.)
     const float2 ew01 = __fadd2_rn(make_float2(d.x, d.y), make_float2(u.x, u.y));
-#endif
-#if H2D_V4_MIX >= 2
-    const float2 ew23 = make_float2(__fadd_rn(d.z, u.z), __fadd_rn(d.w, u.w));
-#else
     const float2 ew23 = __fadd2_rn(make_float2(d.z, d.w), make_float2(u.z, u.w));
-#endif
     const float2 o01 = __ffma2_rn(cx, ew01, g01);
     const float2 o23 = __ffma2_rn(cx, ew23, g23);
     o = make_float4(o01.x, o01.y, o23.x, o23.y);
