@@ -213,6 +213,7 @@ int h2d_plan_run_dataflow(h2d_plan_t* p, int src_parity, int k, int n_epochs, vo
   a.n_strips = (t.cols + a.wv - 1) / a.wv;
   a.n_chunks = (t.rows + R - 1) / R;
   a.n_tasks = a.n_strips * a.n_chunks;
+  a.n_tasks_all = a.n_tasks;
   a.fw = p->fw;
   tk_fill_scratch_ptrs(a, p->scratch);
   a.timeout_ns = p->desc.spin_timeout_ns > 0 ? p->desc.spin_timeout_ns : 10000000000LL;

@@ -239,7 +239,7 @@ static void fill_common(h2d_plan* p, TkArgs& a, int src_parity, int k) {
   a.fw = p->fw;
   tk_fill_scratch_ptrs(a, p->scratch);
   a.timeout_ns = p->desc.spin_timeout_ns > 0 ? p->desc.spin_timeout_ns : 10000000000LL;
-  a.seq = (uint32_t)p->launches;
+  a.seq = p->seq;
   a.debug = tk_debug_flags();
 }
 static void fill_peers(h2d_plan* p, TkArgs& a, int src_parity, uint32_t epoch) {
@@ -289,6 +289,9 @@ void h2d_plan_destroy(h2d_plan_t* p) {
     if (l.dev) cudaFree(l.dev);
   if (p->own_scratch && p->scratch) cudaFree(p->scratch);
   if (p->flow) cudaFree(p->flow);
+  if (p->ev_fork) cudaEventDestroy(p->ev_fork);
+  if (p->ev_join) cudaEventDestroy(p->ev_join);
+  if (p->s_side) cudaStreamDestroy(p->s_side);
   for (cudaEvent_t e : p->ev_pool) cudaEventDestroy(e);
   if (p->s_h2d) cudaStreamDestroy(p->s_h2d);
   if (p->s_d2h) cudaStreamDestroy(p->s_d2h);
@@ -415,14 +418,17 @@ int h2d_plan_launch_ex(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int
 #else
   const bool xtr = p->has_peers || norm != H2D_NORM_NONE;
 #endif
-  tk_fn_t fn = tk_pick(k, p->desc.phys.arith, p->lay, coef_is_reference(p->geo, p->desc.phys.arith), xtr);
+  const bool imm = coef_is_reference(p->geo, p->desc.phys.arith);
+  tk_fn_t fn = tk_pick(k, p->desc.phys.arith, p->lay, imm, xtr);
   if (!fn) return h2d_fail(H2D_EINVAL, "h2d_plan_launch: no kernel for k = %d", k);
   const TaskList& tl = p->lists[round_up4(k) / 4];
+  cudaStream_t st = (cudaStream_t)stream;
 
   TkArgs a;
   fill_common(p, a, src_parity, k);
   a.tasks = tl.dev;
   a.n_tasks = tl.n_tasks;
+  a.n_tasks_all = tl.n_tasks;
   a.n_chunks = p->n_chunks;
   a.chunk_rows = p->chunk_rows;
   a.row_base = 0;
@@ -434,10 +440,49 @@ int h2d_plan_launch_ex(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int
   a.ctl = ctl;
   a.run_if = run_if;
 
+  // A launch with neighbours and no norm is TWO kernels that run side by side: the tasks
+  // that touch the tile edge (first in the task list) go to the halo-forwarding kernel on
+  // the caller's stream, all others to the plain kernel — the one a single GPU runs, with
+  // its registers and instruction footprint — on a side stream forked off and joined back
+  // around the pair.  (One kernel for both kinds ran the interior tasks 7 % (fp32) to 40 %
+  // (strict) slower on B200: 168 instead of 134-144 registers, a stack frame, and an
+  // instruction footprint of 370 KB shared by every warp.)  H2D_SPLIT_LAUNCH=0 disables it.
+  static const bool split_ok = !(getenv("H2D_SPLIT_LAUNCH") && getenv("H2D_SPLIT_LAUNCH")[0] == '0');
+  const int n_edge = tl.n_comm_edge, n_inner = tl.n_tasks - tl.n_comm_edge;
+  tk_fn_t fn_plain = tk_pick(k, p->desc.phys.arith, p->lay, imm, false);
+  if (split_ok && p->has_peers && norm == H2D_NORM_NONE && n_edge > 0 && n_inner > 0 && fn_plain) {
+    if (!p->s_side) {
+      H2D_CUDA_TRY(cudaStreamCreateWithFlags(&p->s_side, cudaStreamNonBlocking));
+      H2D_CUDA_TRY(cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
+      H2D_CUDA_TRY(cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming));
+    }
+    H2D_CUDA_TRY(cudaEventRecord(p->ev_fork, st));
+    H2D_CUDA_TRY(cudaStreamWaitEvent(p->s_side, p->ev_fork, 0));
+    // edge tasks first: their flags gate the neighbours' next launch
+    TkArgs ae = a;
+    ae.n_tasks = n_edge;
+    fn<<<(n_edge + TK_WARPS - 1) / TK_WARPS, TK_WARPS * 32, tk_smem_bytes(p->lay, true), st>>>(p->tmap[src_parity], ae);
+    H2D_CHECK_LAUNCH("tk_kernel (edge tasks)");
+    TkArgs ai = a;
+    ai.tasks = tl.dev + n_edge;
+    ai.n_tasks = n_inner;
+    ai.has_peers = 0;
+    ai.n_comm_edge = 0;
+    fn_plain<<<(n_inner + TK_WARPS - 1) / TK_WARPS, TK_WARPS * 32, tk_smem_bytes(p->lay, false), p->s_side>>>(
+        p->tmap[src_parity], ai);
+    H2D_CHECK_LAUNCH("tk_kernel (interior tasks)");
+    H2D_CUDA_TRY(cudaEventRecord(p->ev_join, p->s_side));
+    H2D_CUDA_TRY(cudaStreamWaitEvent(st, p->ev_join, 0));
+    p->launches += 2;
+    p->seq++;
+    return H2D_OK;
+  }
+
   const int grid = (tl.n_tasks + TK_WARPS - 1) / TK_WARPS;
-  fn<<<grid, TK_WARPS * 32, tk_smem_bytes(p->lay, xtr), (cudaStream_t)stream>>>(p->tmap[src_parity], a);
+  fn<<<grid, TK_WARPS * 32, tk_smem_bytes(p->lay, xtr), st>>>(p->tmap[src_parity], a);
   H2D_CHECK_LAUNCH("tk_kernel");
   p->launches++;
+  p->seq++;
   return H2D_OK;
 }
 
@@ -472,6 +517,7 @@ static int launch_window(h2d_plan* p, int src_parity, int k, int row_base, int r
   a.n_strips = (p->desc.tile.cols + a.wv - 1) / a.wv;
   a.n_chunks = (row_end - row_base + a.chunk_rows - 1) / a.chunk_rows;
   a.n_tasks = a.n_strips * a.n_chunks;
+  a.n_tasks_all = a.n_tasks;
   if (peers) {
     // W / E neighbours only (checked by the caller).  In the flag protocol: the first and the
     // last strip of every chunk (they forward the column bands) and every strip whose stored
@@ -488,6 +534,7 @@ static int launch_window(h2d_plan* p, int src_parity, int k, int row_base, int r
   fn<<<grid, TK_WARPS * 32, tk_smem_bytes(p->lay, peers), st>>>(p->tmap[src_parity], a);
   H2D_CHECK_LAUNCH("tk_kernel (row window)");
   p->launches++;
+  p->seq++;
   return H2D_OK;
 }
 

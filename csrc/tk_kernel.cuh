@@ -129,7 +129,7 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
       if (STRICT && fast) {
         // most tasks of the previous launch were outside the fast path's domain: skip the try
         const unsigned prev = *reinterpret_cast<const volatile unsigned*>(a.strict_fb + (a.seq + 2u) % 3u);
-        if ((int64_t)prev * 4 > (int64_t)a.n_tasks) fast = false;
+        if ((int64_t)prev * 4 > (int64_t)a.n_tasks_all) fast = false;
       }
       // Strict modes: try the fast evaluation unless the previous launch said most tasks are
       // outside its domain; a task whose data is (negative, non-finite or huge anywhere in its

@@ -19,7 +19,11 @@ struct h2d_plan {
   void* scratch = nullptr;          // counters + partials
   bool own_scratch = false;
   int max_ctas = 0;
-  int64_t launches = 0;
+  int64_t launches = 0;             // kernels launched (bench bookkeeping)
+  uint32_t seq = 0;                 // logical launches (one k-step advance of the tile = one)
+  // fork / join of a launch with neighbours: interior tasks run the plain kernel on `s_side`
+  cudaStream_t s_side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   int device = 0;
   bool has_peers = false;
   // lazily created by h2d_plan_run_dataflow: [0] ticket, [64...] done[] per task

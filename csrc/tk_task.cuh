@@ -67,6 +67,7 @@ struct TkArgs {
   float* dst;
   const int2* tasks;     // .x = strip | (comm_edge << 31), .y = chunk
   int32_t n_tasks, n_chunks, chunk_rows, n_comm_edge;
+  int32_t n_tasks_all;   // tasks of the whole logical launch (this kernel may run a part of them)
   int32_t row_base, row_end;   // rows [row_base, row_end) are processed; chunk c starts at row_base + c*R
   int32_t n_strips;            // tasks == nullptr: task -> (task % n_strips, task / n_strips)
   int32_t n_edge_strips;       // tasks == nullptr with peers: strips 0, n_strips-1 (, n_strips-2) come first
