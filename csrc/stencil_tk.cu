@@ -440,14 +440,13 @@ int h2d_plan_launch_ex(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int
   a.ctl = ctl;
   a.run_if = run_if;
 
-  // A launch with neighbours and no norm is TWO kernels that run side by side: the tasks
-  // that touch the tile edge (first in the task list) go to the halo-forwarding kernel on
-  // the caller's stream, all others to the plain kernel — the one a single GPU runs, with
-  // its registers and instruction footprint — on a side stream forked off and joined back
-  // around the pair.  (One kernel for both kinds ran the interior tasks 7 % (fp32) to 40 %
-  // (strict) slower on B200: 168 instead of 134-144 registers, a stack frame, and an
-  // instruction footprint of 370 KB shared by every warp.)  H2D_SPLIT_LAUNCH=0 disables it.
-  static const bool split_ok = !(getenv("H2D_SPLIT_LAUNCH") && getenv("H2D_SPLIT_LAUNCH")[0] == '0');
+  // Optional (H2D_SPLIT_LAUNCH=1): a launch with neighbours and no norm as TWO kernels side by
+  // side — the edge tasks in the forwarding kernel on the caller's stream, all others in the
+  // plain kernel on a side stream forked off and joined back around the pair.  It was built
+  // when forwarding still lived inside the row loop and edge tasks ran several times longer
+  // than interior ones; with the post-pass forwarding one kernel is as fast and costs half
+  // the launches, so the split is off by default.
+  static const bool split_ok = getenv("H2D_SPLIT_LAUNCH") && getenv("H2D_SPLIT_LAUNCH")[0] == '1';
   const int n_edge = tl.n_comm_edge, n_inner = tl.n_tasks - tl.n_comm_edge;
   tk_fn_t fn_plain = tk_pick(k, p->desc.phys.arith, p->lay, imm, false);
   if (split_ok && p->has_peers && norm == H2D_NORM_NONE && n_edge > 0 && n_inner > 0 && fn_plain) {
@@ -838,6 +837,7 @@ int h2d_plan_solve_pipelined_many(h2d_plan_t* const* plans, int n_plans, const f
 }
 
 int64_t h2d_plan_launch_count(const h2d_plan_t* p) { return p ? p->launches : 0; }
+uint32_t* h2d_plan_strict_fallback_ptr(h2d_plan_t* p) { return p ? (uint32_t*)p->scratch + 12 : nullptr; }
 float* h2d_plan_norm_ptr(h2d_plan_t* p) { return p ? (float*)((unsigned*)p->scratch + 2) : nullptr; }
 uint32_t* h2d_plan_fault_ptr(h2d_plan_t* p) { return p ? (uint32_t*)p->scratch + 3 : nullptr; }
 uint64_t* h2d_plan_stats_ptr(h2d_plan_t* p) { return p ? (uint64_t*)((uint32_t*)p->scratch + 8) : nullptr; }

@@ -45,7 +45,6 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
   const int task = (int)blockIdx.x * TK_WARPS + warp;
   const uint32_t ring = smem_u32(smem) + warp * (TK_STAGES * STAGE_BYTES);
   const uint32_t bars = smem_u32(smem) + SMEM_RING + warp * TK_STAGES * 8;
-  const uint32_t we_stage = smem_u32(smem) + SMEM_RING + TK_SMEM_BARS + warp * TK_WE_BYTES;
   if (STRICT && blockIdx.x == 0 && threadIdx.x == 0) a.strict_fb[(a.seq + 1u) % 3u] = 0u;
 
   float acc = 0.f;
@@ -123,7 +122,6 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
       const int jb = ((strip == a.n_strips - 1 && g.cols >= a.wv) ? ((g.cols - a.wv + 3) & ~3) : strip * a.wv) - a.H;
       const bool frozen = (g.x0 + r_lo - K < g.ax_lo) || (g.x0 + r_hi - 1 + K > g.ax_hi) ||
                           (g.y0 + jb < g.ay_lo) || (g.y0 + jb + W - 1 > g.ay_hi);
-      constexpr int XC = XTR ? XM_COMM : XM_NONE, XN = XTR ? XM_NORM : XM_NONE;
       uint32_t track = 0u;
       bool fast = STRICT && !(a.debug & 4);
       if (STRICT && fast) {
@@ -133,25 +131,22 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
       }
       // Strict modes: try the fast evaluation unless the previous launch said most tasks are
       // outside its domain; a task whose data is (negative, non-finite or huge anywhere in its
-      // pipeline) is REDONE with the plain evaluation below — it overwrites every store, local
-      // and remote, before the epoch is published.
+      // pipeline) is REDONE with the plain evaluation below — it overwrites every store before
+      // anything is forwarded or published.
       bool need_slow = STRICT && !fast;
-      int box0 = 0;
+      const bool with_norm = XTR && a.norm != H2D_NORM_NONE;
       if (need_slow) {
-      } else if (XTR && comm_edge && frozen) {
-        acc = run_task<K, ARITH, LAY, IMM, true, XC, STRICT>(&tmap, a, a.dst, strip, chunk, true, ring, bars, we_stage, lane, track);
-      } else if (XTR && comm_edge) {
-        acc = run_task<K, ARITH, LAY, IMM, false, XC, STRICT>(&tmap, a, a.dst, strip, chunk, true, ring, bars, we_stage, lane, track);
-      } else if (XTR && a.norm != H2D_NORM_NONE && frozen) {
-        acc = run_task<K, ARITH, LAY, IMM, true, XN, STRICT>(&tmap, a, a.dst, strip, chunk, false, ring, bars, we_stage, lane, track);
-      } else if (XTR && a.norm != H2D_NORM_NONE) {
-        acc = run_task<K, ARITH, LAY, IMM, false, XN, STRICT>(&tmap, a, a.dst, strip, chunk, false, ring, bars, we_stage, lane, track);
+      } else if (with_norm && frozen) {
+        acc = run_task<K, ARITH, LAY, IMM, true, XTR, STRICT>(&tmap, a, a.dst, strip, chunk, ring, bars, lane, track);
+      } else if (with_norm) {
+        acc = run_task<K, ARITH, LAY, IMM, false, XTR, STRICT>(&tmap, a, a.dst, strip, chunk, ring, bars, lane, track);
       } else if (frozen) {
-        acc = run_task<K, ARITH, LAY, IMM, true, XM_NONE, STRICT>(&tmap, a, a.dst, strip, chunk, false, ring, bars, we_stage, lane, track);
+        acc = run_task<K, ARITH, LAY, IMM, true, false, STRICT>(&tmap, a, a.dst, strip, chunk, ring, bars, lane, track);
       } else {
-        acc = run_task<K, ARITH, LAY, IMM, false, XM_NONE, STRICT>(&tmap, a, a.dst, strip, chunk, false, ring, bars, we_stage, lane, track);
+        acc = run_task<K, ARITH, LAY, IMM, false, false, STRICT>(&tmap, a, a.dst, strip, chunk, ring, bars, lane, track);
       }
       if constexpr (STRICT) {
+        int box0 = 0;
         if (!need_slow && __any_sync(0xffffffffu, track >= STRICT_FAST_LIMIT)) {
           need_slow = true;
           // the ring's mbarriers have completed one phase per box: the second run continues there
@@ -159,15 +154,20 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
           __syncwarp();
         }
         if (need_slow) {
-          // one generic instantiation (boundary selects and extras always compiled in): rare path
-          acc = run_task_v4<K, ARITH, false, true, XC, false>(&tmap, a, a.dst, strip, chunk, comm_edge, ring, bars,
-                                                              we_stage, lane, track, box0);
+          // one generic instantiation (boundary selects and norm always compiled in): rare path
+          acc = run_task_v4<K, ARITH, false, true, XTR, false>(&tmap, a, a.dst, strip, chunk, ring, bars, lane,
+                                                               track, box0);
           // feeds the next launch's decision, whichever way this task got here
           const bool bad = __any_sync(0xffffffffu, track >= STRICT_FAST_LIMIT);
           if (bad && lane == 0) atomicAdd(a.strict_fb + a.seq % 3u, 1u);
         }
       }
 
+      if (comm_edge && !(a.debug & 1)) {
+        // every lane's stores of this chunk are ordered before the copies that read them back
+        __syncwarp();
+        forward_task(a, strip, r_lo, r_hi, lane);
+      }
       if (comm_edge) {
         // Make this warp's peer stores visible system-wide, then count it in; the
         // last edge task of the launch publishes the epoch to every neighbour.

@@ -34,10 +34,7 @@ namespace h2d {
 constexpr int TK_BR = 6;         // rows per TMA box (a multiple of the 3-row register rotation)
 constexpr int TK_STAGES = 4;     // boxes in flight per warp
 constexpr int TK_WARPS = 4;      // warps (tasks) per CTA
-constexpr int TK_WE_ROWS = 16;   // rows of column-halo data staged per remote store
 constexpr int TK_WE_COLS = 32;   // columns forwarded per row and side: one full 128-byte line
-constexpr int TK_WE_Q = TK_WE_COLS / 4;                        // float4 pieces per row and side
-constexpr int TK_WE_BYTES = 2 * TK_WE_ROWS * TK_WE_COLS * 4;   // per warp: W and E side
 constexpr int TK_KMAX = 8;
 
 enum { LAY_V4 = 0, LAY_AB2 = 1, LAY_AB4 = 2, LAY_COUNT = 3 };
@@ -50,9 +47,8 @@ __host__ __device__ constexpr int tk_strip_width(int lay) { return lay == LAY_AB
 __host__ __device__ constexpr int tk_stage_bytes(int lay) { return TK_BR * tk_strip_width(lay) * 4; }
 __host__ __device__ constexpr int tk_smem_ring(int lay) { return TK_WARPS * TK_STAGES * tk_stage_bytes(lay); }
 constexpr int TK_SMEM_BARS = TK_WARPS * TK_STAGES * 8;
-// XTR kernels also carry the per-warp staging block of the batched column halos
-__host__ __device__ constexpr int tk_smem_bytes(int lay, bool xtr) {
-  return tk_smem_ring(lay) + TK_SMEM_BARS + (xtr ? TK_WARPS * TK_WE_BYTES : 0);
+__host__ __device__ constexpr int tk_smem_bytes(int lay, bool /*xtr*/ = false) {
+  return tk_smem_ring(lay) + TK_SMEM_BARS;
 }
 
 struct PeerDev {
@@ -145,16 +141,51 @@ __device__ __forceinline__ float2 lds64(uint32_t addr) {
   return v;
 }
 
-template <int NV> struct Vals { float v[NV]; };
+// ------------------------------------------------- halo forwarding (post-pass)
+// A task that touches the tile edge first computes and stores its chunk like any other
+// task; THEN the warp copies the parts of what it has just stored that lie in a
+// neighbour's ghost margin from its own array into the neighbour's, over NVLink:
+//   N / S (and the corner directions): the rows within `fw` of the tile edge, the columns
+//       this task owns;
+//   W / E: every row of the chunk, the edge columns — as whole 128-byte lines (the 32
+//       outermost columns, exactly the neighbour's margin) whenever the geometry allows,
+//       because partial-line remote writes cost the destination a read-modify-write.
+// Keeping the copies out of the row loop matters more than their own cost: with the
+// forwarding inside the loop (round 1) an edge task carried twice the instructions, a
+// stack frame and spills, ran several times longer than an interior task and set the
+// length of the whole launch (ncu: 21 % of the warp samples on 5 % of the instructions).
+// The reference packs halos with MPI datatypes and sends them with persistent requests
+// (grad1612_mpi_heat.c:140-144,210-227).
+__device__ __forceinline__ void copy_block(const float* src, int64_t spitch, float* dst, int64_t dpitch,
+                                           int nrows, int ncols, int lane) {
+  if (nrows <= 0 || ncols <= 0) return;
+  const bool vec = ((((uintptr_t)src) | ((uintptr_t)dst)) & 15) == 0 && ((spitch | dpitch | ncols) & 3) == 0;
+  if (vec) {
+    const int q = ncols >> 2, total = nrows * q;
+    for (int i = lane; i < total; i += 32) {
+      const int r = i / q, c = (i - r * q) << 2;
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(src + (int64_t)r * spitch + c));
+      *reinterpret_cast<float4*>(dst + (int64_t)r * dpitch + c) = v;
+    }
+  } else {
+    const int total = nrows * ncols;
+    for (int i = lane; i < total; i += 32) {
+      const int r = i / ncols, c = i - r * ncols;
+      dst[(int64_t)r * dpitch + c] = __ldcg(src + (int64_t)r * spitch + c);
+    }
+  }
+}
 
-// --------------------------------------------------- peer forwarding (cold)
-// Store the NV just-computed values of owned row `rho`, columns j0..j0+NV-1, into
-// every neighbour whose ghost margin contains them.  Called only by tasks that
-// touch the tile edge.  `smask` = which of the elements are owned outputs.
-template <int NV>
-__device__ __noinline__ void forward_row(const TkArgs& a, int rho, int j0, Vals<NV> o, int smask,
-                                         bool skip_we) {
+// Columns [c_lo, c_hi) are the ones the task STORED (the shifted last strip stores its whole
+// valid window), [own_lo, c_hi) the ones it owns.
+static __device__ __noinline__ void forward_task(const TkArgs& a, int strip, int r_lo, int r_hi, int lane) {
+  const Geo& g = a.g;
   const int fw = a.fw;
+  const int own_lo = strip * a.wv;
+  const bool first = strip == 0, last = strip == a.n_strips - 1;
+  const int c_hi = last ? g.cols : own_lo + a.wv;
+  // whole-line column bands: usable when the band is float4-aligned in both arrays
+  const bool lines = (g.cols & 3) == 0 && g.cols >= 2 * TK_WE_COLS && fw <= TK_WE_COLS;
 #pragma unroll 1
   for (int d = 0; d < H2D_NDIR; ++d) {
     const PeerDev& p = a.peer[d];
@@ -163,117 +194,24 @@ __device__ __noinline__ void forward_row(const TkArgs& a, int rho, int j0, Vals<
                  : (d == H2D_S || d == H2D_SW || d == H2D_SE) ? 1 : 0;
     const int sy = (d == H2D_W || d == H2D_NW || d == H2D_SW) ? -1
                  : (d == H2D_E || d == H2D_NE || d == H2D_SE) ? 1 : 0;
-    if (sx == 0 && skip_we) continue;   // pure W / E: batched by flush_we()
-    if (sx < 0 && rho >= fw) continue;
-    if (sx > 0 && rho < a.g.rows - fw) continue;
-    int m = 0;
-#pragma unroll
-    for (int e = 0; e < NV; ++e) {
-      const int j = j0 + e;
-      const bool in = (sy == 0) || (sy < 0 ? j < fw : j >= a.g.cols - fw);
-      if (in && ((smask >> e) & 1)) m |= 1 << e;
-    }
-    if (m == 0 || (a.debug & 1)) continue;
-    float* q = p.buf + (int64_t)(a.g.x0 + rho - p.x0 + p.halo_r) * p.pitch +
-               (a.g.y0 + j0 - p.y0 + p.halo_c);
-    if (NV == 4 && m == 15 && (((uintptr_t)q) & 15) == 0) {
-      *reinterpret_cast<float4*>(q) = make_float4(o.v[0], o.v[1], o.v[2], o.v[3]);
-    } else if (NV == 2 && m == 3 && (((uintptr_t)q) & 7) == 0) {
-      *reinterpret_cast<float2*>(q) = make_float2(o.v[0], o.v[1]);
+    int ra = r_lo, rb = r_hi;
+    if (sx < 0) rb = min(rb, fw);
+    if (sx > 0) ra = max(ra, g.rows - fw);
+    int ca, cb;
+    if (sy == 0) {
+      ca = own_lo; cb = c_hi;
     } else {
-#pragma unroll
-      for (int e = 0; e < NV; ++e)
-        if ((m >> e) & 1) q[e] = o.v[e];
+      // the W band belongs to the first strip, the E band to the last one (which has stored
+      // all of it); pure W / E bands travel as whole lines where possible
+      if (sy < 0 ? !first : !last) continue;
+      const int bw = (sx == 0 && lines && p.halo_c >= TK_WE_COLS) ? TK_WE_COLS : fw;
+      ca = sy < 0 ? 0 : g.cols - bw;
+      cb = sy < 0 ? bw : g.cols;
     }
-  }
-}
-
-// Column halos, batched and line-sized.  A column halo is only k floats per row,
-// and 32-byte remote stores are expensive twice over: they stall the issuing warp
-// for about an NVLink round trip each, and a partial-line write costs the
-// destination a read-modify-write (1x2 split: 6770 GLUP/s row by row, 7060 with 16
-// rows per store instruction, vs 8052 for the 2x1 split on two B200).  So each
-// row forwards a whole 128-byte line — the 32 edge columns, which is exactly the
-// neighbour's 32-column margin — parked in shared memory and sent every
-// TK_WE_ROWS rows: lane l sends pieces l, l+32, ... of the 16 x 8 float4 block.
-// `sides` bit 0: this warp holds the W band, bit 1: the E band.
-static __device__ __noinline__ void flush_we(const TkArgs& a, uint32_t stage, int rho0, int count, int sides,
-                                      int lane) {
-  __syncwarp();
-#pragma unroll
-  for (int side = 0; side < 2; ++side) {
-    const PeerDev& p = a.peer[side == 0 ? H2D_W : H2D_E];
-    if (p.buf == nullptr || !((sides >> side) & 1)) continue;
-#pragma unroll
-    for (int it = 0; it < (TK_WE_ROWS * TK_WE_Q) / 32; ++it) {
-      const int idx = it * 32 + lane;
-      const int row = idx / TK_WE_Q, piece = idx % TK_WE_Q;
-      if (row >= count) continue;
-      const float4 v = lds128(stage + (uint32_t)(((side * TK_WE_ROWS + row) * TK_WE_Q + piece) * 16));
-      const int jcol = (side == 0 ? 0 : a.g.cols - TK_WE_COLS) + piece * 4;   // tile-local column
-      float* q = p.buf + (int64_t)(a.g.x0 + rho0 + row - p.x0 + p.halo_r) * p.pitch +
-                 (a.g.y0 + jcol - p.y0 + p.halo_c);
-      *reinterpret_cast<float4*>(q) = v;
-    }
-  }
-  __syncwarp();
-}
-
-// XM: 0 = plain task; 1 = the task feeds the convergence norm; 2 = it also (or
-// only) forwards rows to neighbours.  Warp-uniform and resolved at compile time
-// so the common case carries no overhead in its inner loop.
-constexpr int XM_NONE = 0, XM_NORM = 1, XM_COMM = 2;
-
-// -------------------------------------------------------------------------
-// Per-segment bookkeeping shared by both task bodies.  A segment = NV adjacent
-// columns a lane owns (V4: one segment of 4; AB: one in each half).
-struct SegInfo {
-  int j0;        // tile-local column of element 0
-  int smask;     // which elements are stored (inside the strip's valid window AND owned)
-  int we_off;    // byte offset of this segment inside a staged W/E row block, or -1
-};
-
-// Everything a row of output needs besides the values: built once per task.
-template <int NSEG>
-struct OutCtx {
-  SegInfo seg[NSEG];
-  bool we_batched, we_perrow, we_skip;
-  int we_sides, we_count, we_rho0;
-};
-
-template <int NSEG, int NV, bool COMM>
-__device__ __forceinline__ void setup_out(OutCtx<NSEG>& oc, const TkArgs& a, bool comm_edge, int strip,
-                                          const bool (&seg_valid)[NSEG]) {
-  const Geo& g = a.g;
-  oc.we_batched = false; oc.we_perrow = false; oc.we_skip = false;
-  oc.we_sides = 0; oc.we_count = 0; oc.we_rho0 = 0;
-#pragma unroll
-  for (int s = 0; s < NSEG; ++s) oc.seg[s].we_off = -1;
-  if (COMM) {
-    const bool w_peer = a.peer[H2D_W].buf != nullptr, e_peer = a.peer[H2D_E].buf != nullptr;
-    const bool w_ok = w_peer && a.peer[H2D_W].halo_c >= TK_WE_COLS;
-    const bool e_ok = e_peer && a.peer[H2D_E].halo_c >= TK_WE_COLS;
-    // Batched mode is usable when the 32-column bands are whole segments of single lanes
-    // and fit the neighbour's margin; it then covers EVERY W/E band of the tile (a strip
-    // without band columns simply stages nothing).
-    const bool batched = comm_edge && a.fw <= 8 && (g.cols & 3) == 0 && g.cols >= 2 * TK_WE_COLS &&
-                         (w_ok || e_ok) && (!w_peer || w_ok) && (!e_peer || e_ok);
-    oc.we_skip = batched;
-    oc.we_perrow = comm_edge && !batched && (w_peer || e_peer);
-    if (batched) {
-      // the last strip is shifted to end at the tile edge, so the E band sits in ONE warp
-      if (w_ok && strip == 0) oc.we_sides |= 1;
-      if (e_ok && strip == a.n_strips - 1) oc.we_sides |= 2;
-#pragma unroll
-      for (int s = 0; s < NSEG; ++s) {
-        const int j0 = oc.seg[s].j0;
-        if (!seg_valid[s] || j0 < 0 || j0 + NV > g.cols) continue;   // computed here, owned or not
-        if ((oc.we_sides & 1) && j0 < TK_WE_COLS) oc.seg[s].we_off = j0 * 4;
-        if ((oc.we_sides & 2) && j0 >= g.cols - TK_WE_COLS)
-          oc.seg[s].we_off = TK_WE_ROWS * TK_WE_COLS * 4 + (j0 - (g.cols - TK_WE_COLS)) * 4;
-      }
-      oc.we_batched = oc.we_sides != 0;
-    }
+    if (rb <= ra || cb <= ca) continue;
+    const float* src = a.dst + (int64_t)(g.halo_r + ra) * g.pitch + g.halo_c + ca;
+    float* dst = p.buf + (int64_t)(g.x0 + ra - p.x0 + p.halo_r) * p.pitch + (g.y0 + ca - p.y0 + p.halo_c);
+    copy_block(src, g.pitch, dst, p.pitch, rb - ra, cb - ca, lane);
   }
 }
 
@@ -358,18 +296,16 @@ __device__ __forceinline__ uint32_t umax4(uint32_t t, const float4& v) {
 //                        task body, 4 adjacent columns per lane
 // ============================================================================
 // FROZEN: the footprint contains cells that keep their value (global boundary
-// or outside the grid) -> per-element select.  FAST (strict modes): see above;
-// `track` receives the running maximum of the bit patterns.
-template <int K, int ARITH, bool IMM, bool FROZEN, int XM, bool FAST>
+// or outside the grid) -> per-element select.  NORM: the last level also
+// accumulates (new - old) of the cells the task OWNS (a.norm says which norm).
+// FAST (strict modes): see above; `track` receives the running maximum of the
+// bit patterns.  box0: boxes this warp's ring has already carried in this
+// kernel (a task that is run a second time continues the stage / phase sequence
+// of its mbarriers instead of re-initialising them).
+template <int K, int ARITH, bool IMM, bool FROZEN, bool NORM, bool FAST>
 __device__ __forceinline__ float run_task_v4(const CUtensorMap* tmap, const TkArgs& a, float* dst_base,
-                                             int strip, int chunk, bool comm_edge, uint32_t ring,
-                                             uint32_t bars, uint32_t we_stage, int lane, uint32_t& track,
-                                             int box0 = 0) {
-  // box0: boxes this warp's ring has already carried in this kernel (a task that is run a
-  // second time continues the stage / phase sequence of its mbarriers instead of
-  // re-initialising them)
-  constexpr bool EXTRAS = XM != XM_NONE;   // accumulates the norm (when the launch has one)
-  constexpr bool COMM = XM == XM_COMM;     // forwards to neighbours
+                                             int strip, int chunk, uint32_t ring, uint32_t bars, int lane,
+                                             uint32_t& track, int box0 = 0) {
   constexpr bool TRACK = ARITH != H2D_ARITH_FP32;
   constexpr int W = Lay<LAY_V4>::W;
   constexpr int STAGE_BYTES = TK_BR * W * 4;
@@ -379,10 +315,11 @@ __device__ __forceinline__ float run_task_v4(const CUtensorMap* tmap, const TkAr
   const int r_hi = min(r_lo + R, a.row_end);
   const int n_out = r_hi - r_lo;
   // The last strip is shifted left so that its valid window ends at the tile edge: its
-  // first columns are then computed twice (by it and by its left neighbour) but it OWNS
-  // (stores / reduces) only its own range [own_lo, cols).  No strip is narrow and, what
-  // matters for column halos, the last 32 columns always sit in ONE warp, so the east
-  // band leaves as whole 128-byte lines.
+  // first columns are then computed twice (by it and by its left neighbour).  It STORES its
+  // whole valid window (the doubly computed cells get the same bits from both warps) but
+  // OWNS — reduces, forwards as a row band — only [own_lo, cols).  No strip is narrow and,
+  // what matters for column halos, the last 32 columns always come from ONE warp, so the
+  // east band can leave as whole 128-byte lines.
   const int own_lo = strip * a.wv;
   // (rounded up to a multiple of 4: float4 stores and TMA box origins must stay 16-byte aligned)
   const int vbase = (strip == a.n_strips - 1 && g.cols >= a.wv) ? ((g.cols - a.wv + 3) & ~3) : own_lo;
@@ -395,21 +332,16 @@ __device__ __forceinline__ float run_task_v4(const CUtensorMap* tmap, const TkAr
   const int tc0 = g.halo_c + jbase;      // TMA coordinates of the first box
   const int tc1 = g.halo_r + row0;
 
-  // Which of my 4 columns are stored: inside the strip's valid window and owned.
+  // Which of my 4 columns are stored / owned: inside the strip's valid window and the tile.
   const bool lane_in = (lane * 4 >= a.H) && (lane * 4 < W - a.H);
-  OutCtx<1> oc;
-  oc.seg[0].j0 = j0;
-  oc.seg[0].smask = 0;
+  int smask = 0, nmask = 0;
 #pragma unroll
-  for (int e = 0; e < 4; ++e)
-    if (lane_in && (j0 + e) >= own_lo && (j0 + e) < g.cols) oc.seg[0].smask |= 1 << e;
-  const int smask = oc.seg[0].smask;
+  for (int e = 0; e < 4; ++e) {
+    if (lane_in && (j0 + e) >= vbase && (j0 + e) < g.cols) smask |= 1 << e;
+    if (lane_in && (j0 + e) >= own_lo && (j0 + e) < g.cols) nmask |= 1 << e;
+  }
   const bool st_full = smask == 15;
   const bool st_part = smask != 0 && smask != 15;
-  {
-    const bool sv[1] = {lane_in};
-    setup_out<1, 4, COMM>(oc, a, comm_edge, strip, sv);
-  }
 
   bool act[4] = {true, true, true, true};
   if (FROZEN) {
@@ -447,11 +379,11 @@ __device__ __forceinline__ float run_task_v4(const CUtensorMap* tmap, const TkAr
 
   // One row step: the input row is already in st[0][(PH+2)%3]; levels run
   // 0..K-1, each writing its result straight into the next level's incoming slot.
-  // FWD: this stretch of rows may forward to neighbours (compile-time, so that the
-  // rows of an edge task that forward nothing run the same body as an interior task).
-  auto row_step = [&](auto Ptag, auto Ftag) {
+  // (A "skewed" variant in which level t consumes what level t-1 produced in the
+  // previous row step — K independent levels per step instead of a K-long chain —
+  // was measured 11 % SLOWER on B200: the chain is not the limiter.)
+  auto row_step = [&](auto Ptag) {
     constexpr int PH = decltype(Ptag)::value;
-    constexpr bool FWD = COMM && decltype(Ftag)::value;
     constexpr int iu = PH, ic = (PH + 1) % 3, id = (PH + 2) % 3;
     float4 fin;
     float4 cprev = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -478,7 +410,7 @@ __device__ __forceinline__ float run_task_v4(const CUtensorMap* tmap, const TkAr
         st[t + 1][id] = o;
       } else {
         fin = o;
-        if (EXTRAS) cprev = c;
+        if (NORM) cprev = c;
       }
     }
     if ((unsigned)ro < (unsigned)n_out) {
@@ -490,77 +422,40 @@ __device__ __forceinline__ float run_task_v4(const CUtensorMap* tmap, const TkAr
         if (smask & 4) q[2] = fin.z;
         if (smask & 8) q[3] = fin.w;
       }
-      if (EXTRAS && smask != 0) {
-        // rows outside the N/S bands have nothing to forward once W/E is batched
-        if (FWD && (oc.we_perrow || r_lo + ro < a.fw || r_lo + ro >= g.rows - a.fw)) {
-          Vals<4> v; v.v[0] = fin.x; v.v[1] = fin.y; v.v[2] = fin.z; v.v[3] = fin.w;
-          forward_row<4>(a, r_lo + ro, j0, v, smask, oc.we_skip);
+      if (NORM && nmask != 0) {
+        const float d0 = (nmask & 1) ? fin.x - cprev.x : 0.f;
+        const float d1 = (nmask & 2) ? fin.y - cprev.y : 0.f;
+        const float d2 = (nmask & 4) ? fin.z - cprev.z : 0.f;
+        const float d3 = (nmask & 8) ? fin.w - cprev.w : 0.f;
+        if (a.norm == H2D_NORM_L2SQ) {
+          acc = fmaf(d0, d0, acc); acc = fmaf(d1, d1, acc);
+          acc = fmaf(d2, d2, acc); acc = fmaf(d3, d3, acc);
+        } else {
+          acc = fmax_nan(acc, fmax_nan(fmax_nan(fabsf(d0), fabsf(d1)), fmax_nan(fabsf(d2), fabsf(d3))));
         }
-        if (a.norm != H2D_NORM_NONE) {
-          const float d0 = (smask & 1) ? fin.x - cprev.x : 0.f;
-          const float d1 = (smask & 2) ? fin.y - cprev.y : 0.f;
-          const float d2 = (smask & 4) ? fin.z - cprev.z : 0.f;
-          const float d3 = (smask & 8) ? fin.w - cprev.w : 0.f;
-          if (a.norm == H2D_NORM_L2SQ) {
-            acc = fmaf(d0, d0, acc); acc = fmaf(d1, d1, acc);
-            acc = fmaf(d2, d2, acc); acc = fmaf(d3, d3, acc);
-          } else {
-            acc = fmax_nan(acc, fmax_nan(fmax_nan(fabsf(d0), fabsf(d1)), fmax_nan(fabsf(d2), fabsf(d3))));
-          }
-        }
-      }
-    }
-    if (FWD && oc.we_batched && (unsigned)ro < (unsigned)n_out) {
-      if (oc.we_count == 0) oc.we_rho0 = r_lo + ro;
-      if (oc.seg[0].we_off >= 0) {
-        const uint32_t slot = we_stage + (uint32_t)(oc.seg[0].we_off + oc.we_count * (TK_WE_COLS * 4));
-        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(slot), "f"(fin.x), "f"(fin.y),
-                     "f"(fin.z), "f"(fin.w) : "memory");
-      }
-      ++oc.we_count;
-      if (oc.we_count == TK_WE_ROWS || ro == n_out - 1) {
-        flush_we(a, we_stage, oc.we_rho0, oc.we_count, oc.we_sides, lane);
-        oc.we_count = 0;
       }
     }
     q += g.pitch;
     ++ro;
   };
 
-  auto boxes = [&](auto Ftag, int b_lo, int b_hi) {
 #pragma unroll 1
-    for (int b = b_lo; b < b_hi; ++b) {
-      const int s = (box0 + b) % TK_STAGES;
-      mbar_wait(bars + s * 8, (uint32_t)(((box0 + b) / TK_STAGES) & 1));
-      const uint32_t sbase = ring + s * STAGE_BYTES + lane * 16;
+  for (int b = 0; b < n_blk; ++b) {
+    const int s = (box0 + b) % TK_STAGES;
+    mbar_wait(bars + s * 8, (uint32_t)(((box0 + b) / TK_STAGES) & 1));
+    const uint32_t sbase = ring + s * STAGE_BYTES + lane * 16;
 #pragma unroll 1
-      for (int rr = 0; rr < TK_BR; rr += 3) {
-        st[0][2] = lds128(sbase + rr * (W * 4));
-        row_step(std::integral_constant<int, 0>{}, Ftag);
-        st[0][0] = lds128(sbase + (rr + 1) * (W * 4));
-        row_step(std::integral_constant<int, 1>{}, Ftag);
-        st[0][1] = lds128(sbase + (rr + 2) * (W * 4));
-        row_step(std::integral_constant<int, 2>{}, Ftag);
-      }
-      // Everyone has read stage s: refill it with box b + STAGES.
-      __syncwarp();
-      if (lane == 0 && b + TK_STAGES < n_blk) issue(b + TK_STAGES);
+    for (int rr = 0; rr < TK_BR; rr += 3) {
+      st[0][2] = lds128(sbase + rr * (W * 4));
+      row_step(std::integral_constant<int, 0>{});
+      st[0][0] = lds128(sbase + (rr + 1) * (W * 4));
+      row_step(std::integral_constant<int, 1>{});
+      st[0][1] = lds128(sbase + (rr + 2) * (W * 4));
+      row_step(std::integral_constant<int, 2>{});
     }
-  };
-
-  if (COMM && comm_edge) {
-    // Only the boxes whose output rows lie in the N / S band (or every box, when column
-    // bands are forwarded) run the forwarding body; the stretch between them is plain.
-    int b1 = n_blk, b2 = n_blk;
-    if (!oc.we_batched && !oc.we_perrow) {
-      b1 = r_lo < a.fw ? min(n_blk, (a.fw - r_lo + LAG + TK_BR - 1) / TK_BR) : 0;
-      b2 = r_hi > g.rows - a.fw ? max(b1, min(n_blk, (g.rows - a.fw - r_lo + LAG) / TK_BR)) : n_blk;
-    }
-    boxes(std::true_type{}, 0, b1);
-    boxes(std::false_type{}, b1, b2);
-    boxes(std::true_type{}, b2, n_blk);
-  } else {
-    boxes(std::false_type{}, 0, n_blk);
+    // Everyone has read stage s: refill it with box b + STAGES.
+    __syncwarp();
+    if (lane == 0 && b + TK_STAGES < n_blk) issue(b + TK_STAGES);
   }
   track = trk;
   return acc;
@@ -573,12 +468,9 @@ __device__ __forceinline__ float2 shfl2(float2 v, int src) {
   return make_float2(__shfl_sync(0xffffffffu, v.x, src), __shfl_sync(0xffffffffu, v.y, src));
 }
 
-template <int K, int LAY, bool IMM, bool FROZEN, int XM>
+template <int K, int LAY, bool IMM, bool FROZEN, bool NORM>
 __device__ __forceinline__ float run_task_ab(const CUtensorMap* tmap, const TkArgs& a, float* dst_base,
-                                             int strip, int chunk, bool comm_edge, uint32_t ring,
-                                             uint32_t bars, uint32_t we_stage, int lane) {
-  constexpr bool EXTRAS = XM != XM_NONE;
-  constexpr bool COMM = XM == XM_COMM;
+                                             int strip, int chunk, uint32_t ring, uint32_t bars, int lane) {
   constexpr int NC = Lay<LAY>::NC, W = Lay<LAY>::W, HALF = Lay<LAY>::HALF;
   constexpr int STAGE_BYTES = TK_BR * W * 4;
   const Geo& g = a.g;
@@ -600,17 +492,13 @@ __device__ __forceinline__ float run_task_ab(const CUtensorMap* tmap, const TkAr
   // valid window of the strip = [H, W - H): only the outer side of each half is cut
   const bool validA = lane * NC >= a.H;
   const bool validB = HALF + lane * NC < W - a.H;
-  OutCtx<2> oc;
-  oc.seg[0].j0 = jA; oc.seg[1].j0 = jB;
-  oc.seg[0].smask = 0; oc.seg[1].smask = 0;
+  int smA = 0, smB = 0, nmA = 0, nmB = 0;
 #pragma unroll
   for (int e = 0; e < NC; ++e) {
-    if (validA && (jA + e) >= own_lo && (jA + e) < g.cols) oc.seg[0].smask |= 1 << e;
-    if (validB && (jB + e) >= own_lo && (jB + e) < g.cols) oc.seg[1].smask |= 1 << e;
-  }
-  {
-    const bool sv[2] = {validA, validB};
-    setup_out<2, NC, COMM>(oc, a, comm_edge, strip, sv);
+    if (validA && (jA + e) >= vbase && (jA + e) < g.cols) smA |= 1 << e;
+    if (validB && (jB + e) >= vbase && (jB + e) < g.cols) smB |= 1 << e;
+    if (validA && (jA + e) >= own_lo && (jA + e) < g.cols) nmA |= 1 << e;
+    if (validB && (jB + e) >= own_lo && (jB + e) < g.cols) nmB |= 1 << e;
   }
   constexpr int FULL = (1 << NC) - 1;
 
@@ -677,9 +565,8 @@ __device__ __forceinline__ float run_task_ab(const CUtensorMap* tmap, const TkAr
     }
   };
 
-  auto row_step = [&](auto Ptag, auto Ftag) {
+  auto row_step = [&](auto Ptag) {
     constexpr int PH = decltype(Ptag)::value;
-    constexpr bool FWD = COMM && decltype(Ftag)::value;
     constexpr int iu = PH, ic = (PH + 1) % 3, id = (PH + 2) % 3;
     float2 fin[NC], cprev[NC];
 #pragma unroll
@@ -715,7 +602,7 @@ __device__ __forceinline__ float run_task_ab(const CUtensorMap* tmap, const TkAr
           st[t + 1][id][j] = o;
         } else {
           fin[j] = o;
-          if (EXTRAS) cprev[j] = c;
+          if (NORM) cprev[j] = c;
         }
       }
     }
@@ -723,46 +610,18 @@ __device__ __forceinline__ float run_task_ab(const CUtensorMap* tmap, const TkAr
       float fa[NC], fb[NC];
 #pragma unroll
       for (int j = 0; j < NC; ++j) { fa[j] = fin[j].x; fb[j] = fin[j].y; }
-      store_seg(q, fa, oc.seg[0].smask);
-      store_seg(q + HALF, fb, oc.seg[1].smask);
-      if (EXTRAS) {
-        if (FWD && (oc.we_perrow || r_lo + ro < a.fw || r_lo + ro >= g.rows - a.fw)) {
-          Vals<NC> va, vb;
+      store_seg(q, fa, smA);
+      store_seg(q + HALF, fb, smB);
+      if (NORM) {
 #pragma unroll
-          for (int j = 0; j < NC; ++j) { va.v[j] = fa[j]; vb.v[j] = fb[j]; }
-          if (oc.seg[0].smask) forward_row<NC>(a, r_lo + ro, jA, va, oc.seg[0].smask, oc.we_skip);
-          if (oc.seg[1].smask) forward_row<NC>(a, r_lo + ro, jB, vb, oc.seg[1].smask, oc.we_skip);
-        }
-        if (a.norm != H2D_NORM_NONE) {
-#pragma unroll
-          for (int j = 0; j < NC; ++j) {
-            const float da = ((oc.seg[0].smask >> j) & 1) ? fin[j].x - cprev[j].x : 0.f;
-            const float db = ((oc.seg[1].smask >> j) & 1) ? fin[j].y - cprev[j].y : 0.f;
-            if (a.norm == H2D_NORM_L2SQ) {
-              acc = fmaf(da, da, acc); acc = fmaf(db, db, acc);
-            } else {
-              acc = fmax_nan(acc, fmax_nan(fabsf(da), fabsf(db)));
-            }
+        for (int j = 0; j < NC; ++j) {
+          const float da = ((nmA >> j) & 1) ? fin[j].x - cprev[j].x : 0.f;
+          const float db = ((nmB >> j) & 1) ? fin[j].y - cprev[j].y : 0.f;
+          if (a.norm == H2D_NORM_L2SQ) {
+            acc = fmaf(da, da, acc); acc = fmaf(db, db, acc);
+          } else {
+            acc = fmax_nan(acc, fmax_nan(fabsf(da), fabsf(db)));
           }
-        }
-      }
-      if (FWD && oc.we_batched) {
-        if (oc.we_count == 0) oc.we_rho0 = r_lo + ro;
-#pragma unroll
-        for (int s = 0; s < 2; ++s) {
-          if (oc.seg[s].we_off < 0) continue;
-          const uint32_t slot = we_stage + (uint32_t)(oc.seg[s].we_off + oc.we_count * (TK_WE_COLS * 4));
-          const float* v = s == 0 ? fa : fb;
-          if constexpr (NC == 4)
-            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(slot), "f"(v[0]), "f"(v[1]),
-                         "f"(v[2]), "f"(v[3]) : "memory");
-          else
-            asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(slot), "f"(v[0]), "f"(v[1]) : "memory");
-        }
-        ++oc.we_count;
-        if (oc.we_count == TK_WE_ROWS || ro == n_out - 1) {
-          flush_we(a, we_stage, oc.we_rho0, oc.we_count, oc.we_sides, lane);
-          oc.we_count = 0;
         }
       }
     }
@@ -770,54 +629,37 @@ __device__ __forceinline__ float run_task_ab(const CUtensorMap* tmap, const TkAr
     ++ro;
   };
 
-  auto boxes = [&](auto Ftag, int b_lo, int b_hi) {
 #pragma unroll 1
-    for (int b = b_lo; b < b_hi; ++b) {
-      const int s = b % TK_STAGES;
-      mbar_wait(bars + s * 8, (uint32_t)((b / TK_STAGES) & 1));
-      const uint32_t sbase = ring + s * STAGE_BYTES + lane * (NC * 4);
+  for (int b = 0; b < n_blk; ++b) {
+    const int s = b % TK_STAGES;
+    mbar_wait(bars + s * 8, (uint32_t)((b / TK_STAGES) & 1));
+    const uint32_t sbase = ring + s * STAGE_BYTES + lane * (NC * 4);
 #pragma unroll 1
-      for (int rr = 0; rr < TK_BR; rr += 3) {
-        load_row(sbase + rr * (W * 4), st[0][2]);
-        row_step(std::integral_constant<int, 0>{}, Ftag);
-        load_row(sbase + (rr + 1) * (W * 4), st[0][0]);
-        row_step(std::integral_constant<int, 1>{}, Ftag);
-        load_row(sbase + (rr + 2) * (W * 4), st[0][1]);
-        row_step(std::integral_constant<int, 2>{}, Ftag);
-      }
-      __syncwarp();
-      if (lane == 0 && b + TK_STAGES < n_blk) issue(b + TK_STAGES);
+    for (int rr = 0; rr < TK_BR; rr += 3) {
+      load_row(sbase + rr * (W * 4), st[0][2]);
+      row_step(std::integral_constant<int, 0>{});
+      load_row(sbase + (rr + 1) * (W * 4), st[0][0]);
+      row_step(std::integral_constant<int, 1>{});
+      load_row(sbase + (rr + 2) * (W * 4), st[0][1]);
+      row_step(std::integral_constant<int, 2>{});
     }
-  };
-
-  if (COMM && comm_edge) {
-    int b1 = n_blk, b2 = n_blk;
-    if (!oc.we_batched && !oc.we_perrow) {
-      b1 = r_lo < a.fw ? min(n_blk, (a.fw - r_lo + LAG + TK_BR - 1) / TK_BR) : 0;
-      b2 = r_hi > g.rows - a.fw ? max(b1, min(n_blk, (g.rows - a.fw - r_lo + LAG) / TK_BR)) : n_blk;
-    }
-    boxes(std::true_type{}, 0, b1);
-    boxes(std::false_type{}, b1, b2);
-    boxes(std::true_type{}, b2, n_blk);
-  } else {
-    boxes(std::false_type{}, 0, n_blk);
+    __syncwarp();
+    if (lane == 0 && b + TK_STAGES < n_blk) issue(b + TK_STAGES);
   }
   return acc;
 }
 
 // One entry point for both families.  `track` is meaningful for strict modes only.
-template <int K, int ARITH, int LAY, bool IMM, bool FROZEN, int XM, bool FAST>
+template <int K, int ARITH, int LAY, bool IMM, bool FROZEN, bool NORM, bool FAST>
 __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs& a, float* dst_base,
-                                          int strip, int chunk, bool comm_edge, uint32_t ring,
-                                          uint32_t bars, uint32_t we_stage, int lane, uint32_t& track) {
+                                          int strip, int chunk, uint32_t ring, uint32_t bars, int lane,
+                                          uint32_t& track) {
   if constexpr (LAY == LAY_V4) {
-    return run_task_v4<K, ARITH, IMM, FROZEN, XM, FAST>(tmap, a, dst_base, strip, chunk, comm_edge, ring, bars,
-                                                        we_stage, lane, track);
+    return run_task_v4<K, ARITH, IMM, FROZEN, NORM, FAST>(tmap, a, dst_base, strip, chunk, ring, bars, lane, track);
   } else {
     static_assert(ARITH == H2D_ARITH_FP32 || LAY == LAY_V4, "packed layouts are fp32 only");
     track = 0u;
-    return run_task_ab<K, LAY, IMM, FROZEN, XM>(tmap, a, dst_base, strip, chunk, comm_edge, ring, bars,
-                                                we_stage, lane);
+    return run_task_ab<K, LAY, IMM, FROZEN, NORM>(tmap, a, dst_base, strip, chunk, ring, bars, lane);
   }
 }
 

@@ -162,6 +162,8 @@ def cuda():
             lib.h2d_plan_fault_ptr.restype = vp
             lib.h2d_plan_stats_ptr.argtypes = [vp]
             lib.h2d_plan_stats_ptr.restype = vp
+            lib.h2d_plan_strict_fallback_ptr.argtypes = [vp]
+            lib.h2d_plan_strict_fallback_ptr.restype = vp
             lib.h2d_resident_fits.argtypes = [C.c_int32, C.c_int32]
             lib.h2d_resident_run.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int64, C.c_int64, P(Phys), vp]
             lib.h2d_norm_scratch_bytes.argtypes = [P(Tile)]

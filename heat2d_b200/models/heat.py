@@ -195,6 +195,11 @@ class TileEngine:
     def fault(self) -> int:
         return int(self._fault.item())
 
+    def strict_fallbacks(self):
+        """Tasks of the last three launches that left the fast strict evaluation (3 counters)."""
+        t = tensor_from_ptr(self.plan.strict_fallback_ptr, (3,), torch.int32, self.field.device)
+        return [int(x) for x in t.tolist()]
+
     def halo_wait_stats(self):
         """(microseconds edge tasks spent blocked on neighbour flags, number of blocking waits)
         accumulated since the plan was created."""

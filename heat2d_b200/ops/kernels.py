@@ -320,6 +320,10 @@ class Plan:
     def stats_ptr(self) -> int:
         return int(self._lib.h2d_plan_stats_ptr(self._h))
 
+    @property
+    def strict_fallback_ptr(self) -> int:
+        return int(self._lib.h2d_plan_strict_fallback_ptr(self._h))
+
     def close(self):
         if getattr(self, "_h", None):
             self._lib.h2d_plan_destroy(self._h)

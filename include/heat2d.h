@@ -304,6 +304,11 @@ uint32_t* h2d_plan_fault_ptr(h2d_plan_t* plan);
  * counterpart of the MPI_Waitall row of the reference's mpiP profile (Report.pdf p35-37). */
 uint64_t* h2d_plan_stats_ptr(h2d_plan_t* plan);
 
+/* Device address of three rotating 32-bit counters (strict arithmetic only): tasks of the
+ * last launches whose data was outside the domain of the fast evaluation and were computed
+ * with the plain one (slot = logical launch number % 3). */
+uint32_t* h2d_plan_strict_fallback_ptr(h2d_plan_t* plan);
+
 /* ---- resident solver: whole grid in the shared memory of one cluster ------ */
 /* All `steps` steps in ONE launch; halo rows travel between the CTAs of the
  * cluster through distributed shared memory.  Returns H2D_EINVAL if the grid
