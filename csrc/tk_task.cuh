@@ -156,16 +156,45 @@ __device__ __forceinline__ float2 lds64(uint32_t addr) {
 // length of the whole launch (ncu: 21 % of the warp samples on 5 % of the instructions).
 // The reference packs halos with MPI datatypes and sends them with persistent requests
 // (grad1612_mpi_heat.c:140-144,210-227).
+// Remote stores issued by a warp complete one NVLink round trip at a time (measured: a copy
+// loop of 137 store instructions took ~400 us, 2.9 us each, and a 1 x 2 split ran at
+// 6460 instead of 8680 GLUP/s because every launch waited for it).  So the copy is handed to
+// the bulk-copy engine instead: the warp gathers the rows into its (now idle) TMA ring in
+// shared memory and one lane issues one asynchronous shared -> global bulk store per row
+// (cp.async.bulk, plain addresses: no tensor map, no multicast, and only STORES ever target
+// a neighbour's memory); nobody waits for a round trip until the task's final
+// wait_group.  Unaligned geometries (odd tile origins) fall back to plain stores.
+__device__ __forceinline__ void bulk_store_row(float* dst, uint32_t src_smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src_smem), "r"(bytes)
+               : "memory");
+}
 __device__ __forceinline__ void copy_block(const float* src, int64_t spitch, float* dst, int64_t dpitch,
-                                           int nrows, int ncols, int lane) {
+                                           int nrows, int ncols, int lane, uint32_t stage, int stage_bytes) {
   if (nrows <= 0 || ncols <= 0) return;
   const bool vec = ((((uintptr_t)src) | ((uintptr_t)dst)) & 15) == 0 && ((spitch | dpitch | ncols) & 3) == 0;
-  if (vec) {
-    const int q = ncols >> 2, total = nrows * q;
-    for (int i = lane; i < total; i += 32) {
-      const int r = i / q, c = (i - r * q) << 2;
-      const float4 v = __ldcg(reinterpret_cast<const float4*>(src + (int64_t)r * spitch + c));
-      *reinterpret_cast<float4*>(dst + (int64_t)r * dpitch + c) = v;
+  if (vec && ncols * 4 <= stage_bytes) {
+    const int q = ncols >> 2;                       // float4 pieces per row
+    const int rows_per_round = stage_bytes / (ncols * 4);
+    for (int r0 = 0; r0 < nrows; r0 += rows_per_round) {
+      const int n = min(rows_per_round, nrows - r0);
+      // the previous round's bulk stores must have finished reading the staging area
+      if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      __syncwarp();
+      const int total = n * q;
+#pragma unroll 4
+      for (int i = lane; i < total; i += 32) {
+        const int r = i / q, c = (i - r * q) << 2;
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(src + (int64_t)(r0 + r) * spitch + c));
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(stage + (uint32_t)(i * 16)), "f"(v.x),
+                     "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> async-proxy reads
+      __syncwarp();
+      if (lane == 0) {
+        for (int r = 0; r < n; ++r)
+          bulk_store_row(dst + (int64_t)(r0 + r) * dpitch, stage + (uint32_t)(r * ncols * 4), (uint32_t)(ncols * 4));
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
     }
   } else {
     const int total = nrows * ncols;
@@ -178,7 +207,8 @@ __device__ __forceinline__ void copy_block(const float* src, int64_t spitch, flo
 
 // Columns [c_lo, c_hi) are the ones the task STORED (the shifted last strip stores its whole
 // valid window), [own_lo, c_hi) the ones it owns.
-static __device__ __noinline__ void forward_task(const TkArgs& a, int strip, int r_lo, int r_hi, int lane) {
+static __device__ __noinline__ void forward_task(const TkArgs& a, int strip, int r_lo, int r_hi, int lane,
+                                                 uint32_t stage, int stage_bytes) {
   const Geo& g = a.g;
   const int fw = a.fw;
   const int own_lo = strip * a.wv;
@@ -211,8 +241,15 @@ static __device__ __noinline__ void forward_task(const TkArgs& a, int strip, int
     if (rb <= ra || cb <= ca) continue;
     const float* src = a.dst + (int64_t)(g.halo_r + ra) * g.pitch + g.halo_c + ca;
     float* dst = p.buf + (int64_t)(g.x0 + ra - p.x0 + p.halo_r) * p.pitch + (g.y0 + ca - p.y0 + p.halo_c);
-    copy_block(src, g.pitch, dst, p.pitch, rb - ra, cb - ca, lane);
+    copy_block(src, g.pitch, dst, p.pitch, rb - ra, cb - ca, lane, stage, stage_bytes);
   }
+  // all bulk stores of this task have been performed (their writes are visible to this thread,
+  // which then fences and counts the task in)
+  if (lane == 0) {
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    asm volatile("fence.proxy.async;" ::: "memory");
+  }
+  __syncwarp();
 }
 
 // ============================================================================
