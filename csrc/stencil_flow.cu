@@ -140,9 +140,9 @@ tk_flow_kernel(const __grid_constant__ CUtensorMap tmap0, const __grid_constant_
   float* dst = pa.dst[e & 1];
   uint32_t track = 0u;
   if (frozen) {
-    run_task_v4<K, ARITH, IMM, true, false, false>(tm, a, dst, strip, chunk, ring, bars, lane, track);
+    run_task_v4<K, ARITH, IMM, true, false, false>(tm, a, dst, strip, r_lo, r_hi, ring, bars, lane, track);
   } else {
-    run_task_v4<K, ARITH, IMM, false, false, false>(tm, a, dst, strip, chunk, ring, bars, lane, track);
+    run_task_v4<K, ARITH, IMM, false, false, false>(tm, a, dst, strip, r_lo, r_hi, ring, bars, lane, track);
   }
   flow_publish(pa, task, pa.base + (uint32_t)e + 1u, lane);
 }

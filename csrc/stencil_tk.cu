@@ -197,24 +197,47 @@ static int make_tmap(CUtensorMap* out, float* base, const h2d_tile_t& t, int lay
   return H2D_OK;
 }
 
+// Chunk size of the strips that forward column bands.  A remote store instruction costs its
+// warp an NVLink round trip (~3 us) however much it moves, so a column band of R rows costs
+// R / 4 round trips at the END of its task: with R in the hundreds that is longer than the
+// rest of the launch, and since a rank's next launch waits for its neighbours' edge tasks the
+// launch period becomes twice that (1 x 2 on two B200: 6460 instead of 8680 GLUP/s).  Short
+// chunks put the same copies into many tasks that run side by side in the first wave; the
+// extra pipeline fill (2K rows per chunk) is paid on 2 strips in ~150 only.
+static int edge_chunk_rows(const h2d_plan* p, int R, int kmax) {
+  const bool we = p->desc.peer[H2D_W].buf[0] || p->desc.peer[H2D_E].buf[0];
+  if (!we) return R;
+  const int slots = sm_count() * warps_per_sm(kmax, p->lay);
+  int Re = (int)((4LL * p->desc.tile.rows + slots - 1) / slots);   // <= slots / 2 tasks on 2 strips
+  Re = (Re + 7) & ~7;
+  const char* e = getenv("H2D_EDGE_CHUNK");
+  if (e && atoi(e) >= 8) Re = atoi(e);
+  if (Re < 32) Re = 32;
+  if (Re < kmax) Re = kmax;
+  return Re < R ? Re : R;
+}
+
 static int build_task_list(h2d_plan* p, int H, TaskList* out) {
   const h2d_tile_t& t = p->desc.tile;
   const int wv = tk_strip_width(p->lay) - 2 * H;
   const int ns = (t.cols + wv - 1) / wv;
   const int nc = p->n_chunks;
-  const int R = p->chunk_rows;
+  const int R = p->chunk_rows, Re = p->chunk_rows_edge;
+  const int nce = (t.rows + Re - 1) / Re;
   const int fw = p->fw;
   std::vector<int2> edge, inner;
-  edge.reserve((size_t)2 * (ns + nc));
+  edge.reserve((size_t)2 * (ns + nc + nce));
   inner.reserve((size_t)ns * nc);
-  for (int c = 0; c < nc; ++c) {
-    const int r_lo = c * R, r_hi = (c == nc - 1) ? t.rows : r_lo + R;
-    const bool row_edge = r_lo < fw || r_hi > t.rows - fw;
-    for (int s = 0; s < ns; ++s) {
-      const int j_lo = s * wv, j_hi = (j_lo + wv < t.cols) ? j_lo + wv : t.cols;
-      const bool col_edge = j_lo < fw || j_hi > t.cols - fw;
+  for (int s = 0; s < ns; ++s) {
+    const int j_lo = s * wv, j_hi = (j_lo + wv < t.cols) ? j_lo + wv : t.cols;
+    const bool col_edge = j_lo < fw || j_hi > t.cols - fw;
+    const bool shorter = col_edge && Re < R;    // this strip forwards (or waits for) column bands
+    const int rr = shorter ? Re : R, n = shorter ? nce : nc;
+    for (int c = 0; c < n; ++c) {
+      const int r_lo = c * rr, r_hi = (c == n - 1) ? t.rows : r_lo + rr;
+      const bool row_edge = r_lo < fw || r_hi > t.rows - fw;
       if (row_edge || col_edge)
-        edge.push_back(make_int2((int)((unsigned)s | 0x80000000u), c));
+        edge.push_back(make_int2((int)((unsigned)s | 0x80000000u | (shorter ? 0x40000000u : 0u)), c));
       else
         inner.push_back(make_int2(s, c));
     }
@@ -280,6 +303,7 @@ size_t h2d_plan_scratch_bytes(const h2d_tile_t* tile, int32_t kmax, int32_t chun
     if (m1 > mt) mt = m1;
     if (m2 > mt) mt = m2;
   }
+  mt += 3 * ((tile->rows + 31) / 32);   // column-band strips in chunks of >= 32 rows
   return scratch_layout_bytes(mt);
 }
 
@@ -356,6 +380,9 @@ h2d_plan_t* h2d_plan_create(const h2d_plan_desc_t* d) {
   plan_counts(&t, d->kmax, d->chunk_rows, p->lay, &p->n_chunks, &max_tasks, min_waves);
   p->chunk_rows = d->chunk_rows > 0 ? d->chunk_rows : choose_chunk_rows(t.rows, t.cols, d->kmax, p->lay, min_waves);
   if (p->n_chunks == 1) p->chunk_rows = t.rows;
+  p->chunk_rows_edge = edge_chunk_rows(p, p->chunk_rows, d->kmax);
+  // (the column-band strips may hold more, shorter tasks than plan_counts() assumed)
+  max_tasks += 3 * ((t.rows + p->chunk_rows_edge - 1) / p->chunk_rows_edge);
   p->fw = d->kmax;
   if (p->fw > t.rows) p->fw = t.rows;
   if (p->fw > t.cols) p->fw = t.cols;
@@ -431,6 +458,7 @@ int h2d_plan_launch_ex(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int
   a.n_tasks_all = tl.n_tasks;
   a.n_chunks = p->n_chunks;
   a.chunk_rows = p->chunk_rows;
+  a.chunk_rows_edge = p->chunk_rows_edge;
   a.row_base = 0;
   a.row_end = p->desc.tile.rows;
   a.n_strips = tl.n_strips;
@@ -515,20 +543,26 @@ static int launch_window(h2d_plan* p, int src_parity, int k, int row_base, int r
   a.row_end = row_end;
   a.n_strips = (p->desc.tile.cols + a.wv - 1) / a.wv;
   a.n_chunks = (row_end - row_base + a.chunk_rows - 1) / a.chunk_rows;
+  a.chunk_rows_edge = a.chunk_rows;
+  a.n_chunks_edge = a.n_chunks;
   a.n_tasks = a.n_strips * a.n_chunks;
-  a.n_tasks_all = a.n_tasks;
   if (peers) {
     // W / E neighbours only (checked by the caller).  In the flag protocol: the first and the
     // last strip of every chunk (they forward the column bands) and every strip whose stored
     // cells depend on a ghost column — with the last strip shifted to end at the tile edge that
-    // can only be the one before it, when the last strip owns fewer than fw columns.
+    // can only be the one before it, when the last strip owns fewer than fw columns.  These
+    // strips run in short chunks (see edge_chunk_rows).
     const int ns = a.n_strips;
     int ne = ns >= 2 ? 2 : 1;
     if (ns >= 3 && p->desc.tile.cols - (ns - 1) * a.wv < a.fw) ne = 3;
     a.n_edge_strips = ne;
-    a.n_comm_edge = ne * a.n_chunks;
+    a.chunk_rows_edge = p->chunk_rows_edge < a.chunk_rows ? p->chunk_rows_edge : a.chunk_rows;
+    a.n_chunks_edge = (row_end - row_base + a.chunk_rows_edge - 1) / a.chunk_rows_edge;
+    a.n_comm_edge = ne * a.n_chunks_edge;
+    a.n_tasks = a.n_comm_edge + (ns - ne) * a.n_chunks;
     fill_peers(p, a, src_parity, epoch);
   }
+  a.n_tasks_all = a.n_tasks;
   const int grid = (a.n_tasks + TK_WARPS - 1) / TK_WARPS;
   fn<<<grid, TK_WARPS * 32, tk_smem_bytes(p->lay, peers), st>>>(p->tmap[src_parity], a);
   H2D_CHECK_LAUNCH("tk_kernel (row window)");

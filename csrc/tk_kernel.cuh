@@ -61,14 +61,14 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
     } else if (XTR && a.has_peers) {
       // Row window of a tile with W / E neighbours (pipelined solve): no task list; the
       // tasks of the strips that take part in the flag protocol — the first and the last
-      // (they hold the 32-column bands) and, when the last strip owns fewer than k columns,
-      // the one before it (its results depend on the E ghost columns) — come first, chunk
-      // by chunk, then the interior strips.
-      const int ns = a.n_strips, ne = a.n_edge_strips, n_edge = ne * a.n_chunks;
+      // (they forward the 32-column bands) and, when the last strip owns fewer than k columns,
+      // the one before it (its results depend on the E ghost columns) — come first, in short
+      // chunks, then the interior strips.
+      const int ns = a.n_strips, ne = a.n_edge_strips, n_edge = ne * a.n_chunks_edge;
       if (task < n_edge) {
         const int i = task % ne;
         const int s = i == 0 ? 0 : (i == 1 ? ns - 1 : ns - 2);
-        tk = make_int2((int)(((unsigned)s) | 0x80000000u), task / ne);
+        tk = make_int2((int)(((unsigned)s) | 0xc0000000u), task / ne);
       } else {
         const int t2 = task - n_edge;
         tk = make_int2(1 + t2 % (ns - ne), t2 / (ns - ne));
@@ -76,9 +76,11 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
     } else {
       tk = make_int2(task % a.n_strips, task / a.n_strips);
     }
-    const int strip = tk.x & 0x7fffffff;
+    const int strip = tk.x & 0x3fffffff;
     const bool comm_edge = XTR && (tk.x < 0) && a.has_peers;
-    const int chunk = tk.y;
+    const int R = (tk.x & 0x40000000) ? a.chunk_rows_edge : a.chunk_rows;
+    const int r_lo = a.row_base + tk.y * R;
+    const int r_hi = min(r_lo + R, a.row_end);
 
     if (comm_edge && (a.debug & 2)) {
       // Stress mode (race detection): shake the order in which ranks reach
@@ -116,9 +118,6 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
     if (alive) {
       // Does the footprint (all K levels) stay inside the updated region?
       const Geo& g = a.g;
-      const int R = a.chunk_rows;
-      const int r_lo = a.row_base + chunk * R;
-      const int r_hi = min(r_lo + R, a.row_end);
       const int jb = ((strip == a.n_strips - 1 && g.cols >= a.wv) ? ((g.cols - a.wv + 3) & ~3) : strip * a.wv) - a.H;
       const bool frozen = (g.x0 + r_lo - K < g.ax_lo) || (g.x0 + r_hi - 1 + K > g.ax_hi) ||
                           (g.y0 + jb < g.ay_lo) || (g.y0 + jb + W - 1 > g.ay_hi);
@@ -137,13 +136,13 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
       const bool with_norm = XTR && a.norm != H2D_NORM_NONE;
       if (need_slow) {
       } else if (with_norm && frozen) {
-        acc = run_task<K, ARITH, LAY, IMM, true, XTR, STRICT>(&tmap, a, a.dst, strip, chunk, ring, bars, lane, track);
+        acc = run_task<K, ARITH, LAY, IMM, true, XTR, STRICT>(&tmap, a, a.dst, strip, r_lo, r_hi, ring, bars, lane, track);
       } else if (with_norm) {
-        acc = run_task<K, ARITH, LAY, IMM, false, XTR, STRICT>(&tmap, a, a.dst, strip, chunk, ring, bars, lane, track);
+        acc = run_task<K, ARITH, LAY, IMM, false, XTR, STRICT>(&tmap, a, a.dst, strip, r_lo, r_hi, ring, bars, lane, track);
       } else if (frozen) {
-        acc = run_task<K, ARITH, LAY, IMM, true, false, STRICT>(&tmap, a, a.dst, strip, chunk, ring, bars, lane, track);
+        acc = run_task<K, ARITH, LAY, IMM, true, false, STRICT>(&tmap, a, a.dst, strip, r_lo, r_hi, ring, bars, lane, track);
       } else {
-        acc = run_task<K, ARITH, LAY, IMM, false, false, STRICT>(&tmap, a, a.dst, strip, chunk, ring, bars, lane, track);
+        acc = run_task<K, ARITH, LAY, IMM, false, false, STRICT>(&tmap, a, a.dst, strip, r_lo, r_hi, ring, bars, lane, track);
       }
       if constexpr (STRICT) {
         int box0 = 0;
@@ -155,7 +154,7 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
         }
         if (need_slow) {
           // one generic instantiation (boundary selects and norm always compiled in): rare path
-          acc = run_task_v4<K, ARITH, false, true, XTR, false>(&tmap, a, a.dst, strip, chunk, ring, bars, lane,
+          acc = run_task_v4<K, ARITH, false, true, XTR, false>(&tmap, a, a.dst, strip, r_lo, r_hi, ring, bars, lane,
                                                                track, box0);
           // feeds the next launch's decision, whichever way this task got here
           const bool bad = __any_sync(0xffffffffu, track >= STRICT_FAST_LIMIT);
@@ -166,7 +165,7 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
       if (comm_edge && !(a.debug & 1)) {
         // every lane's stores of this chunk are ordered before the copies that read them back
         __syncwarp();
-        forward_task(a, strip, r_lo, r_hi, lane, ring, TK_STAGES * STAGE_BYTES);
+        forward_task(a, strip, r_lo, r_hi, lane);
       }
       if (comm_edge) {
         // Make this warp's peer stores visible system-wide, then count it in; the

@@ -15,6 +15,7 @@ struct h2d_plan {
   int lay = h2d::LAY_V4;            // lane layout of this plan's kernels (tk_task.cuh)
   CUtensorMap tmap[2];
   int n_chunks = 0, chunk_rows = 0, fw = 0;
+  int chunk_rows_edge = 0;          // chunk size of the strips that forward column bands (== chunk_rows without W/E peers)
   TaskList lists[h2d::TK_KMAX / 4 + 1];  // index H/4 (H = 4, 8)
   void* scratch = nullptr;          // counters + partials
   bool own_scratch = false;

@@ -61,9 +61,12 @@ struct PeerDev {
 struct TkArgs {
   Geo g;
   float* dst;
-  const int2* tasks;     // .x = strip | (comm_edge << 31), .y = chunk
+  const int2* tasks;     // .x = strip | (comm_edge << 31) | (short chunks << 30), .y = chunk
   int32_t n_tasks, n_chunks, chunk_rows, n_comm_edge;
   int32_t n_tasks_all;   // tasks of the whole logical launch (this kernel may run a part of them)
+  // Tasks of the strips that forward column bands (bit 30 of tasks[].x, or the edge strips of
+  // a row window) use shorter chunks: chunk c of such a strip starts at row_base + c * chunk_rows_edge
+  int32_t chunk_rows_edge, n_chunks_edge;
   int32_t row_base, row_end;   // rows [row_base, row_end) are processed; chunk c starts at row_base + c*R
   int32_t n_strips;            // tasks == nullptr: task -> (task % n_strips, task / n_strips)
   int32_t n_edge_strips;       // tasks == nullptr with peers: strips 0, n_strips-1 (, n_strips-2) come first
@@ -156,45 +159,24 @@ __device__ __forceinline__ float2 lds64(uint32_t addr) {
 // length of the whole launch (ncu: 21 % of the warp samples on 5 % of the instructions).
 // The reference packs halos with MPI datatypes and sends them with persistent requests
 // (grad1612_mpi_heat.c:140-144,210-227).
-// Remote stores issued by a warp complete one NVLink round trip at a time (measured: a copy
-// loop of 137 store instructions took ~400 us, 2.9 us each, and a 1 x 2 split ran at
-// 6460 instead of 8680 GLUP/s because every launch waited for it).  So the copy is handed to
-// the bulk-copy engine instead: the warp gathers the rows into its (now idle) TMA ring in
-// shared memory and one lane issues one asynchronous shared -> global bulk store per row
-// (cp.async.bulk, plain addresses: no tensor map, no multicast, and only STORES ever target
-// a neighbour's memory); nobody waits for a round trip until the task's final
-// wait_group.  Unaligned geometries (odd tile origins) fall back to plain stores.
-__device__ __forceinline__ void bulk_store_row(float* dst, uint32_t src_smem, uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src_smem), "r"(bytes)
-               : "memory");
-}
+// A remote store instruction completes one NVLink round trip at a time for the warp that
+// issued it (measured on B200: ~2.9 us per instruction, whatever its size; shared -> global
+// bulk stores of the copy engine serialise the same way, ~2.3 us per 128-byte row, and were
+// slower).  So a store moves as much as a warp can — 512 bytes, 4 rows of a column band —
+// and the tasks that forward column bands are kept SHORT (TkArgs::chunk_rows_edge): many
+// short edge tasks copy side by side in the first wave of a launch, instead of a few long
+// ones serialising hundreds of round trips at the end of theirs.
 __device__ __forceinline__ void copy_block(const float* src, int64_t spitch, float* dst, int64_t dpitch,
-                                           int nrows, int ncols, int lane, uint32_t stage, int stage_bytes) {
+                                           int nrows, int ncols, int lane) {
   if (nrows <= 0 || ncols <= 0) return;
   const bool vec = ((((uintptr_t)src) | ((uintptr_t)dst)) & 15) == 0 && ((spitch | dpitch | ncols) & 3) == 0;
-  if (vec && ncols * 4 <= stage_bytes) {
-    const int q = ncols >> 2;                       // float4 pieces per row
-    const int rows_per_round = stage_bytes / (ncols * 4);
-    for (int r0 = 0; r0 < nrows; r0 += rows_per_round) {
-      const int n = min(rows_per_round, nrows - r0);
-      // the previous round's bulk stores must have finished reading the staging area
-      if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-      __syncwarp();
-      const int total = n * q;
+  if (vec) {
+    const int q = ncols >> 2, total = nrows * q;
 #pragma unroll 4
-      for (int i = lane; i < total; i += 32) {
-        const int r = i / q, c = (i - r * q) << 2;
-        const float4 v = __ldcg(reinterpret_cast<const float4*>(src + (int64_t)(r0 + r) * spitch + c));
-        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(stage + (uint32_t)(i * 16)), "f"(v.x),
-                     "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
-      }
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> async-proxy reads
-      __syncwarp();
-      if (lane == 0) {
-        for (int r = 0; r < n; ++r)
-          bulk_store_row(dst + (int64_t)(r0 + r) * dpitch, stage + (uint32_t)(r * ncols * 4), (uint32_t)(ncols * 4));
-        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-      }
+    for (int i = lane; i < total; i += 32) {
+      const int r = i / q, c = (i - r * q) << 2;
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(src + (int64_t)r * spitch + c));
+      *reinterpret_cast<float4*>(dst + (int64_t)r * dpitch + c) = v;
     }
   } else {
     const int total = nrows * ncols;
@@ -207,8 +189,7 @@ __device__ __forceinline__ void copy_block(const float* src, int64_t spitch, flo
 
 // Columns [c_lo, c_hi) are the ones the task STORED (the shifted last strip stores its whole
 // valid window), [own_lo, c_hi) the ones it owns.
-static __device__ __noinline__ void forward_task(const TkArgs& a, int strip, int r_lo, int r_hi, int lane,
-                                                 uint32_t stage, int stage_bytes) {
+static __device__ __noinline__ void forward_task(const TkArgs& a, int strip, int r_lo, int r_hi, int lane) {
   const Geo& g = a.g;
   const int fw = a.fw;
   const int own_lo = strip * a.wv;
@@ -241,15 +222,8 @@ static __device__ __noinline__ void forward_task(const TkArgs& a, int strip, int
     if (rb <= ra || cb <= ca) continue;
     const float* src = a.dst + (int64_t)(g.halo_r + ra) * g.pitch + g.halo_c + ca;
     float* dst = p.buf + (int64_t)(g.x0 + ra - p.x0 + p.halo_r) * p.pitch + (g.y0 + ca - p.y0 + p.halo_c);
-    copy_block(src, g.pitch, dst, p.pitch, rb - ra, cb - ca, lane, stage, stage_bytes);
+    copy_block(src, g.pitch, dst, p.pitch, rb - ra, cb - ca, lane);
   }
-  // all bulk stores of this task have been performed (their writes are visible to this thread,
-  // which then fences and counts the task in)
-  if (lane == 0) {
-    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-    asm volatile("fence.proxy.async;" ::: "memory");
-  }
-  __syncwarp();
 }
 
 // ============================================================================
@@ -341,15 +315,12 @@ __device__ __forceinline__ uint32_t umax4(uint32_t t, const float4& v) {
 // of its mbarriers instead of re-initialising them).
 template <int K, int ARITH, bool IMM, bool FROZEN, bool NORM, bool FAST>
 __device__ __forceinline__ float run_task_v4(const CUtensorMap* tmap, const TkArgs& a, float* dst_base,
-                                             int strip, int chunk, uint32_t ring, uint32_t bars, int lane,
+                                             int strip, int r_lo, int r_hi, uint32_t ring, uint32_t bars, int lane,
                                              uint32_t& track, int box0 = 0) {
   constexpr bool TRACK = ARITH != H2D_ARITH_FP32;
   constexpr int W = Lay<LAY_V4>::W;
   constexpr int STAGE_BYTES = TK_BR * W * 4;
   const Geo& g = a.g;
-  const int R = a.chunk_rows;
-  const int r_lo = a.row_base + chunk * R;
-  const int r_hi = min(r_lo + R, a.row_end);
   const int n_out = r_hi - r_lo;
   // The last strip is shifted left so that its valid window ends at the tile edge: its
   // first columns are then computed twice (by it and by its left neighbour).  It STORES its
@@ -507,13 +478,10 @@ __device__ __forceinline__ float2 shfl2(float2 v, int src) {
 
 template <int K, int LAY, bool IMM, bool FROZEN, bool NORM>
 __device__ __forceinline__ float run_task_ab(const CUtensorMap* tmap, const TkArgs& a, float* dst_base,
-                                             int strip, int chunk, uint32_t ring, uint32_t bars, int lane) {
+                                             int strip, int r_lo, int r_hi, uint32_t ring, uint32_t bars, int lane) {
   constexpr int NC = Lay<LAY>::NC, W = Lay<LAY>::W, HALF = Lay<LAY>::HALF;
   constexpr int STAGE_BYTES = TK_BR * W * 4;
   const Geo& g = a.g;
-  const int R = a.chunk_rows;
-  const int r_lo = a.row_base + chunk * R;
-  const int r_hi = min(r_lo + R, a.row_end);
   const int n_out = r_hi - r_lo;
   const int own_lo = strip * a.wv;
   const int vbase = (strip == a.n_strips - 1 && g.cols >= a.wv) ? ((g.cols - a.wv + 3) & ~3) : own_lo;
@@ -689,14 +657,14 @@ __device__ __forceinline__ float run_task_ab(const CUtensorMap* tmap, const TkAr
 // One entry point for both families.  `track` is meaningful for strict modes only.
 template <int K, int ARITH, int LAY, bool IMM, bool FROZEN, bool NORM, bool FAST>
 __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs& a, float* dst_base,
-                                          int strip, int chunk, uint32_t ring, uint32_t bars, int lane,
+                                          int strip, int r_lo, int r_hi, uint32_t ring, uint32_t bars, int lane,
                                           uint32_t& track) {
   if constexpr (LAY == LAY_V4) {
-    return run_task_v4<K, ARITH, IMM, FROZEN, NORM, FAST>(tmap, a, dst_base, strip, chunk, ring, bars, lane, track);
+    return run_task_v4<K, ARITH, IMM, FROZEN, NORM, FAST>(tmap, a, dst_base, strip, r_lo, r_hi, ring, bars, lane, track);
   } else {
     static_assert(ARITH == H2D_ARITH_FP32 || LAY == LAY_V4, "packed layouts are fp32 only");
     track = 0u;
-    return run_task_ab<K, LAY, IMM, FROZEN, NORM>(tmap, a, dst_base, strip, chunk, ring, bars, lane);
+    return run_task_ab<K, LAY, IMM, FROZEN, NORM>(tmap, a, dst_base, strip, r_lo, r_hi, ring, bars, lane);
   }
 }
 
