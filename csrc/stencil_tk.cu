@@ -62,7 +62,10 @@ int tk_debug_flags() {
     const char* e = getenv("H2D_DEBUG_NOFWD");
     const char* d = getenv("H2D_DEBUG_DELAY");
     const char* f = getenv("H2D_STRICT_FAST");
-    dbg = ((e && e[0] == '1') ? 1 : 0) | ((d && d[0] == '1') ? 2 : 0) | ((f && f[0] == '0') ? 4 : 0);
+    const char* b = getenv("H2D_FWD_BULK");    // row bands through the bulk-copy engine (default on)
+    const char* l = getenv("H2D_FWD_LINES");   // column bands as whole 128-byte lines
+    dbg = ((e && e[0] == '1') ? 1 : 0) | ((d && d[0] == '1') ? 2 : 0) | ((f && f[0] == '0') ? 4 : 0) |
+          ((b && b[0] == '0') ? 0 : 8) | ((l && l[0] == '1') ? 16 : 0);
   }
   return dbg;
 }

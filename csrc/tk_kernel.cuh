@@ -165,7 +165,7 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
       if (comm_edge && !(a.debug & 1)) {
         // every lane's stores of this chunk are ordered before the copies that read them back
         __syncwarp();
-        forward_task(a, strip, r_lo, r_hi, lane);
+        forward_task(a, strip, r_lo, r_hi, lane, ring, TK_STAGES * STAGE_BYTES);
       }
       if (comm_edge) {
         // Make this warp's peer stores visible system-wide, then count it in; the

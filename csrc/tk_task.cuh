@@ -95,6 +95,8 @@ struct TkArgs {
   int32_t debug;   // bit 0: skip the peer stores (timing experiments only; H2D_DEBUG_NOFWD=1)
                    // bit 1: random per-task delays around the flag protocol (H2D_DEBUG_DELAY=1)
                    // bit 2: strict modes never take the fast path (H2D_STRICT_FAST=0)
+                   // bit 3: row bands go through the bulk-copy engine (H2D_FWD_BULK, default 1)
+                   // bit 4: column bands as whole 128-byte lines (H2D_FWD_LINES=1)
 };
 
 // ------------------------------------------------------------ PTX wrappers
@@ -187,16 +189,52 @@ __device__ __forceinline__ void copy_block(const float* src, int64_t spitch, flo
   }
 }
 
+// The same copy through the bulk-copy engine: the warp gathers the rows into its (now idle)
+// TMA ring in shared memory and one lane issues one asynchronous shared -> global bulk store
+// per row (cp.async.bulk with plain addresses: no tensor map, no multicast, and only STORES
+// ever target a neighbour's memory).  The engine also takes ~2.3 us per remote row, one after
+// the other, but it does so on its own: worth it for long rows (N / S bands), hopeless for
+// 32-byte column-band rows.
+__device__ __forceinline__ void copy_block_bulk(const float* src, int64_t spitch, float* dst, int64_t dpitch,
+                                                int nrows, int ncols, int lane, uint32_t stage, int stage_bytes) {
+  const int q = ncols >> 2;                       // float4 pieces per row
+  const int rows_per_round = stage_bytes / (ncols * 4);
+  for (int r0 = 0; r0 < nrows; r0 += rows_per_round) {
+    const int n = min(rows_per_round, nrows - r0);
+    // the previous round's bulk stores must have finished reading the staging area
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    __syncwarp();
+    const int total = n * q;
+#pragma unroll 4
+    for (int i = lane; i < total; i += 32) {
+      const int r = i / q, c = (i - r * q) << 2;
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(src + (int64_t)(r0 + r) * spitch + c));
+      asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(stage + (uint32_t)(i * 16)), "f"(v.x),
+                   "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> async-proxy reads
+    __syncwarp();
+    if (lane == 0) {
+      for (int r = 0; r < n; ++r)
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst + (int64_t)(r0 + r) * dpitch),
+                     "r"(stage + (uint32_t)(r * ncols * 4)), "r"((uint32_t)(ncols * 4)) : "memory");
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+  }
+}
+
 // Columns [c_lo, c_hi) are the ones the task STORED (the shifted last strip stores its whole
 // valid window), [own_lo, c_hi) the ones it owns.
-static __device__ __noinline__ void forward_task(const TkArgs& a, int strip, int r_lo, int r_hi, int lane) {
+static __device__ __noinline__ void forward_task(const TkArgs& a, int strip, int r_lo, int r_hi, int lane,
+                                                 uint32_t stage, int stage_bytes) {
   const Geo& g = a.g;
   const int fw = a.fw;
   const int own_lo = strip * a.wv;
   const bool first = strip == 0, last = strip == a.n_strips - 1;
   const int c_hi = last ? g.cols : own_lo + a.wv;
-  // whole-line column bands: usable when the band is float4-aligned in both arrays
-  const bool lines = (g.cols & 3) == 0 && g.cols >= 2 * TK_WE_COLS && fw <= TK_WE_COLS;
+  // whole-line column bands (debug bit 4): 4x the store instructions of exact-width bands
+  const bool lines = (a.debug & 16) && (g.cols & 3) == 0 && g.cols >= 2 * TK_WE_COLS && fw <= TK_WE_COLS;
+  bool used_bulk = false;
 #pragma unroll 1
   for (int d = 0; d < H2D_NDIR; ++d) {
     const PeerDev& p = a.peer[d];
@@ -222,7 +260,22 @@ static __device__ __noinline__ void forward_task(const TkArgs& a, int strip, int
     if (rb <= ra || cb <= ca) continue;
     const float* src = a.dst + (int64_t)(g.halo_r + ra) * g.pitch + g.halo_c + ca;
     float* dst = p.buf + (int64_t)(g.x0 + ra - p.x0 + p.halo_r) * p.pitch + (g.y0 + ca - p.y0 + p.halo_c);
-    copy_block(src, g.pitch, dst, p.pitch, rb - ra, cb - ca, lane);
+    const int nr = rb - ra, ncl = cb - ca;
+    const bool vec = ((((uintptr_t)src) | ((uintptr_t)dst)) & 15) == 0 && ((g.pitch | p.pitch | ncl) & 3) == 0;
+    if ((a.debug & 8) && vec && ncl >= 64 && ncl * 4 <= stage_bytes) {
+      copy_block_bulk(src, g.pitch, dst, p.pitch, nr, ncl, lane, stage, stage_bytes);
+      used_bulk = true;
+    } else {
+      copy_block(src, g.pitch, dst, p.pitch, nr, ncl, lane);
+    }
+  }
+  if (used_bulk) {
+    // all bulk stores of this task have been performed before the task is counted in
+    if (lane == 0) {
+      asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+      asm volatile("fence.proxy.async;" ::: "memory");
+    }
+    __syncwarp();
   }
 }
 
