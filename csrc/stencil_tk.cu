@@ -57,17 +57,14 @@ bool coef_is_reference(const Geo& g, int arith) {
 // per-task delays around the flag protocol (stress test); H2D_STRICT_FAST=0: strict modes
 // always use the plain F2F evaluation.
 int tk_debug_flags() {
-  static int dbg = -1;
-  if (dbg < 0) {
-    const char* e = getenv("H2D_DEBUG_NOFWD");
-    const char* d = getenv("H2D_DEBUG_DELAY");
-    const char* f = getenv("H2D_STRICT_FAST");
-    const char* b = getenv("H2D_FWD_BULK");    // row bands through the bulk-copy engine (default on)
-    const char* l = getenv("H2D_FWD_LINES");   // column bands as whole 128-byte lines
-    dbg = ((e && e[0] == '1') ? 1 : 0) | ((d && d[0] == '1') ? 2 : 0) | ((f && f[0] == '0') ? 4 : 0) |
-          ((b && b[0] == '0') ? 0 : 8) | ((l && l[0] == '1') ? 16 : 0);
-  }
-  return dbg;
+  // read on every launch: sweeps switch these between runs of one process
+  const char* e = getenv("H2D_DEBUG_NOFWD");
+  const char* d = getenv("H2D_DEBUG_DELAY");
+  const char* f = getenv("H2D_STRICT_FAST");
+  const char* b = getenv("H2D_FWD_BULK");    // row bands through the bulk-copy engine (default on)
+  const char* l = getenv("H2D_FWD_LINES");   // column bands as whole 128-byte lines
+  return ((e && e[0] == '1') ? 1 : 0) | ((d && d[0] == '1') ? 2 : 0) | ((f && f[0] == '0') ? 4 : 0) |
+         ((b && b[0] == '0') ? 0 : 8) | ((l && l[0] == '1') ? 16 : 0);
 }
 
 }  // namespace h2d
@@ -200,22 +197,17 @@ static int make_tmap(CUtensorMap* out, float* base, const h2d_tile_t& t, int lay
   return H2D_OK;
 }
 
-// Chunk size of the strips that forward column bands.  A remote store instruction costs its
-// warp an NVLink round trip (~3 us) however much it moves, so a column band of R rows costs
-// R / 4 round trips at the END of its task: with R in the hundreds that is longer than the
-// rest of the launch, and since a rank's next launch waits for its neighbours' edge tasks the
-// launch period becomes twice that (1 x 2 on two B200: 6460 instead of 8680 GLUP/s).  Short
-// chunks put the same copies into many tasks that run side by side in the first wave; the
-// extra pipeline fill (2K rows per chunk) is paid on 2 strips in ~150 only.
+// Chunk size of the strips that forward column bands: a tuning hook (H2D_EDGE_CHUNK=rows).
+// Shorter chunks spread the column-band copies over more, shorter tasks; measured on two B200
+// (1 x 2, 32768^2) that made things WORSE (6008 vs 6492 GLUP/s): the cost of a column band is
+// not in the issuing warp (whole 128-byte lines and exact 32-byte rows cost the same, and
+// without the copies 1 x 2 runs at the 2 x 1 speed, 8625), it is the row-strided remote
+// writes themselves.  Default: the same chunks as every other strip.
 static int edge_chunk_rows(const h2d_plan* p, int R, int kmax) {
   const bool we = p->desc.peer[H2D_W].buf[0] || p->desc.peer[H2D_E].buf[0];
-  if (!we) return R;
-  const int slots = sm_count() * warps_per_sm(kmax, p->lay);
-  int Re = (int)((4LL * p->desc.tile.rows + slots - 1) / slots);   // <= slots / 2 tasks on 2 strips
-  Re = (Re + 7) & ~7;
   const char* e = getenv("H2D_EDGE_CHUNK");
-  if (e && atoi(e) >= 8) Re = atoi(e);
-  if (Re < 32) Re = 32;
+  if (!we || !e || atoi(e) < 8) return R;
+  int Re = atoi(e);
   if (Re < kmax) Re = kmax;
   return Re < R ? Re : R;
 }

@@ -36,6 +36,7 @@ def main():
     ap.add_argument("--conv", action="store_true")
     ap.add_argument("--reps", type=int, default=2)
     ap.add_argument("--tag", default="")
+    ap.add_argument("--bulk", default="1", help="comma list of 0/1: row bands through the bulk-copy engine")
     a = ap.parse_args()
     rank, world, local, device = init_distributed()
     layouts = [tuple(int(v) for v in l.split("x")) for l in a.layouts.split(",") if l] or [(world, 1)]
@@ -48,11 +49,12 @@ def main():
             for px, py in layouts:
                 if px * py != world:
                     continue
-                for mw in a.min_waves.split(","):
+                for mw, bulk in [(m, b) for m in a.min_waves.split(",") for b in a.bulk.split(",")]:
                     os.environ["H2D_MIN_WAVES"] = mw
+                    os.environ["H2D_FWD_BULK"] = bulk
                     cls = HaloExchangeSolver if backend == "nccl-halo" else DistributedHeat2DSolver
                     rec = {"n_gpus": world, "grid": n, "steps": a.steps, "k": a.k, "backend": backend, "arith": arith,
-                           "px": px, "py": py, "min_waves": int(mw), "conv": a.conv}
+                           "px": px, "py": py, "min_waves": int(mw), "bulk": int(bulk), "conv": a.conv}
                     try:
                         # correctness on a small case with the same process grid
                         vcfg = HeatConfig(nx=1536, ny=2048, steps=2 * a.k + 3, px=px, py=py, k=a.k, halo=max(a.k, 8),
