@@ -307,12 +307,13 @@ def _e2e(a, cfg, solver, world, rank, device, steps, verified_pipe):
                    f"{steps} steps, device -> pinned host copy of the whole final field; bytes are "
                    "the job totals divided by the step count; one untimed call of the same API first",
            "how": how}
-    # what the PCIe links alone would allow: both directions run concurrently
-    peaks = _peaks()
-    pcie = peaks.get("pcie_h2d_gbs_per_gpu")
-    if pcie:
-        floor_s = host_in.numel() * 4 / (pcie * 1e9)
+    # what the host <-> device links of this box allow with all N ranks copying at once, both
+    # directions concurrently (profiles/pcie_peaks.json, measured with tools/pcie_probe.py)
+    peak = (_peaks().get("by_n") or {}).get(str(world)) or {}
+    if peak.get("both_total"):
+        floor_s = (host_in.numel() + host_out.numel()) * 4 * world / (peak["both_total"] * 1e9)
         out["pcie_floor_seconds"] = floor_s
+        out["pcie_both_directions_gbs_measured"] = peak["both_total"]
         out["e2e_roofline"] = floor_s / e2e_s
     if strip is not None:
         strip.close()

@@ -36,7 +36,7 @@ CUDA_SOURCES = ["basic_kernels.cu", "stencil_tk.cu", "stencil_flow.cu", "residen
 TK_INSTANCES = [(f"tk_a{a}_l{l}_x{x}", a, l, x)
                 for a, ls in ((0, (0, 1, 2)), (1, (0,)), (2, (0,))) for l in ls for x in (0, 1)]
 # defaults baked into the library (both can be overridden at run time, see stencil_tk.cu)
-TK_DEFAULTS = ["-DH2D_DEFAULT_FP32_LAYOUT=0", "-DH2D_DEFAULT_MIN_WAVES=4"]
+TK_DEFAULTS = ["-DH2D_DEFAULT_FP32_LAYOUT=0", "-DH2D_DEFAULT_MIN_WAVES=2"]
 
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",

@@ -38,10 +38,12 @@ def test_small_grids_use_short_chunks():
 
 
 def test_plans_with_peers_keep_edge_tasks_short():
-    # >= 4 waves per launch: the edge tasks (first wave) gate the neighbours' next launch
+    # >= 2 waves per launch: the edge tasks (first wave) gate the neighbours' next launch.
+    # (4 was the round-1 rule; on 8 B200 2 is 2-3 % faster: 30979 vs 30360 GLUP/s at 8 x 1,
+    # profiles/scaling_sweep_n8.jsonl)
     for rows, cols in [(32768, 8192), (4096, 32768), (8192, 16384)]:
         R = chunk_rows(rows, cols, peers=True)
-        assert waves(rows, cols, R) > 3.0
+        assert waves(rows, cols, R) > 1.5
         assert R <= chunk_rows(rows, cols, peers=False)
 
 
