@@ -48,6 +48,8 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("-k", type=int, help="time steps per launch / halo exchange (1..8)")
     ap.add_argument("--backend", choices=BACKENDS)
     ap.add_argument("--chunk-rows", type=int)
+    ap.add_argument("--layout", choices=["auto", "v4", "ab2", "ab4"],
+                    help="lane layout of the fp32 kernels (same bits; v4 is the measured best on B200)")
     ap.add_argument("--dataflow", action="store_true",
                     help="single tile, no convergence: all sweeps in one dataflow launch")
     ap.add_argument("--threads", type=int, help="NUMTHREADS (cpu backend)")
@@ -67,7 +69,7 @@ def config_from_args(a) -> HeatConfig:
     over = {}
     for name in ("nx", "ny", "steps", "px", "py", "interval", "eps", "norm", "cx", "cy", "boundary", "arith",
                  "init", "dump", "out_dir", "k", "backend", "chunk_rows", "threads", "restart", "start_step",
-                 "conv_mode"):
+                 "conv_mode", "layout"):
         v = getattr(a, name, None)
         if v is not None:
             over[name] = v
