@@ -293,6 +293,7 @@ def _e2e(a, cfg, solver, world, rank, device, steps, verified_pipe):
 
         def fn():
             f.buf[solver.parity].copy_(host_in, non_blocking=True)       # H2D of this rank's inputs
+            solver.seed_colbufs()                                        # ghost columns came with the upload
             solver.barrier()                                             # peers' ghosts must be in place
             solver.run(steps)
             host_out.copy_(f.owned(solver.parity), non_blocking=True)    # D2H of the result

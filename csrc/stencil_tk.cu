@@ -67,6 +67,18 @@ int tk_debug_flags() {
          ((b && b[0] == '0') ? 0 : 8) | ((l && l[0] == '1') ? 16 : 0);
 }
 
+// margins of a freshly filled padded array -> this rank's packed column-ghost buffers
+__global__ void seed_colbuf_kernel(const float* __restrict__ base, Geo g, int fw, float* w, float* e) {
+  const int64_t n = (int64_t)g.rows * TK_CW;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x) {
+    const int r = (int)(t / TK_CW), j = (int)(t % TK_CW);
+    if (j >= fw) continue;
+    const float* row = base + (int64_t)(g.halo_r + r) * g.pitch + g.halo_c;
+    if (w) w[t] = row[j - fw];
+    if (e) e[t] = row[g.cols + j];
+  }
+}
+
 }  // namespace h2d
 
 using namespace h2d;
@@ -252,6 +264,9 @@ static void fill_common(h2d_plan* p, TkArgs& a, int src_parity, int k) {
   const int H = round_up4(k);
   a.g = p->geo;
   a.dst = p->desc.buf[1 - src_parity];
+  a.src = p->desc.buf[src_parity];
+  a.colbuf_in[0] = p->desc.colbuf_in[0][src_parity];
+  a.colbuf_in[1] = p->desc.colbuf_in[1][src_parity];
   a.H = H;
   a.wv = tk_strip_width(p->lay) - 2 * H;
   a.fw = p->fw;
@@ -265,6 +280,7 @@ static void fill_peers(h2d_plan* p, TkArgs& a, int src_parity, uint32_t epoch) {
   for (int d = 0; d < H2D_NDIR; ++d) {
     const h2d_peer_t& pr = p->desc.peer[d];
     a.peer[d].buf = pr.buf[1 - src_parity];
+    a.peer[d].colbuf = pr.colbuf[1 - src_parity];
     a.peer[d].flag = pr.flag;
     a.peer[d].x0 = pr.x0; a.peer[d].y0 = pr.y0;
     a.peer[d].halo_r = pr.halo_r; a.peer[d].halo_c = pr.halo_c;
@@ -354,6 +370,11 @@ h2d_plan_t* h2d_plan_create(const h2d_plan_desc_t* d) {
       }
       has_peers = true;
     }
+  for (int side = 0; side < 2; ++side)
+    if ((d->colbuf_in[side][0] == nullptr) != (d->colbuf_in[side][1] == nullptr)) {
+      h2d_fail(H2D_EINVAL, "h2d_plan_create: colbuf_in[%d] needs both parities", side);
+      return nullptr;
+    }
   if (has_peers && !d->flags_in) {
     h2d_fail(H2D_EINVAL, "h2d_plan_create: peers given but flags_in is null");
     return nullptr;
@@ -422,6 +443,19 @@ h2d_plan_t* h2d_plan_create(const h2d_plan_desc_t* d) {
 }
 
 int32_t h2d_plan_layout(const h2d_plan_t* p) { return p ? p->lay + 1 : 0; }
+
+int h2d_plan_seed_colbuf(h2d_plan_t* p, int parity, void* stream) {
+  if (!p || (parity != 0 && parity != 1)) return h2d_fail(H2D_EINVAL, "h2d_plan_seed_colbuf: bad argument");
+  const h2d_tile_t& t = p->desc.tile;
+  float* w = p->desc.colbuf_in[0][parity];
+  float* e = p->desc.colbuf_in[1][parity];
+  if (!w && !e) return H2D_OK;
+  const int64_t n = (int64_t)t.rows * TK_CW;
+  const int blocks = (int)((n + 255) / 256 > 1184 ? 1184 : (n + 255) / 256);
+  seed_colbuf_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(p->desc.buf[parity], p->geo, p->fw, w, e);
+  H2D_CHECK_LAUNCH("seed_colbuf_kernel");
+  return H2D_OK;
+}
 
 int h2d_plan_launch(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int norm, void* stream) {
   return h2d_plan_launch_ex(p, src_parity, k, epoch, norm, nullptr, 0u, stream);
@@ -525,7 +559,7 @@ int h2d_plan_run_many(h2d_plan_t* const* plans, int n_plans, int src_parity, int
 // One k-step launch restricted to owned rows [row_base, row_end) of a single tile
 // (no norm): tasks are enumerated arithmetically, chunk c starts at row_base + c * R.
 static int launch_window(h2d_plan* p, int src_parity, int k, int row_base, int row_end, int chunk_rows,
-                         cudaStream_t st, uint32_t epoch = 0u) {
+                         cudaStream_t st, uint32_t epoch = 0u, bool unpack = true) {
   if (row_end <= row_base) return H2D_OK;
   const bool peers = p->has_peers;
   tk_fn_t fn = tk_pick(k, p->desc.phys.arith, p->lay, coef_is_reference(p->geo, p->desc.phys.arith), peers);
@@ -533,6 +567,7 @@ static int launch_window(h2d_plan* p, int src_parity, int k, int row_base, int r
   TkArgs a;
   fill_common(p, a, src_parity, k);
   a.tasks = nullptr;
+  if (!unpack) a.colbuf_in[0] = a.colbuf_in[1] = nullptr;   // the ghost columns of this launch came from the host
   a.chunk_rows = chunk_rows;
   a.row_base = row_base;
   a.row_end = row_end;
@@ -794,7 +829,7 @@ static int pipelined_solve(PipeRank* qs, int n, int64_t steps, int k, int block_
       // equal depths (20 steps at k = 8 -> 7 + 7 + 6): a trailing shallow launch would be HBM-bound
       const int kk = (int)(steps / L) + (e < (int)(steps % L) ? 1 : 0);
       for (int i = 0; i < n; ++i)
-        if (int rc = launch_window(qs[i].p, e & 1, kk, (int)lo, (int)hi, qs[i].R, cs, epoch)) return rc;
+        if (int rc = launch_window(qs[i].p, e & 1, kk, (int)lo, (int)hi, qs[i].R, cs, epoch, e > 0)) return rc;
       ++epoch;   // one epoch per issued window, on every rank alike
     }
     // rows below b_hi - S*(L-1) now hold the final field

@@ -121,6 +121,11 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
       const int jb = ((strip == a.n_strips - 1 && g.cols >= a.wv) ? ((g.cols - a.wv + 3) & ~3) : strip * a.wv) - a.H;
       const bool frozen = (g.x0 + r_lo - K < g.ax_lo) || (g.x0 + r_hi - 1 + K > g.ax_hi) ||
                           (g.y0 + jb < g.ay_lo) || (g.y0 + jb + W - 1 > g.ay_hi);
+      if (XTR && comm_edge && (a.colbuf_in[0] != nullptr || a.colbuf_in[1] != nullptr)) {
+        // ghost columns arrive packed: put the rows this task reads into the source array's margins
+        const bool west = jb < 0, east = jb + W > g.cols;
+        if (west || east) unpack_colbuf(a, west, east, r_lo - K, r_hi + K, lane);
+      }
       uint32_t track = 0u;
       bool fast = STRICT && !(a.debug & 4);
       if (STRICT && fast) {

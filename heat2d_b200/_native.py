@@ -34,6 +34,7 @@ class Tile(C.Structure):
         ("rows", C.c_int32), ("cols", C.c_int32),
         ("halo_r", C.c_int32), ("halo_c", C.c_int32),
         ("pitch", C.c_int64),
+        ("colbuf", C.c_void_p * 2),
     ]
 
 
@@ -48,6 +49,7 @@ class Peer(C.Structure):
         ("x0", C.c_int32), ("y0", C.c_int32),
         ("halo_r", C.c_int32), ("halo_c", C.c_int32),
         ("pitch", C.c_int64),
+        ("colbuf", C.c_void_p * 2),
     ]
 
 
@@ -64,6 +66,7 @@ class PlanDesc(C.Structure):
         ("spin_timeout_ns", C.c_int64),
         ("layout", C.c_int32),
         ("reserved", C.c_int32),
+        ("colbuf_in", (C.c_void_p * 2) * 2),
     ]
 
 
@@ -144,6 +147,7 @@ def cuda():
             lib.h2d_plan_strip_width.restype = C.c_int32
             lib.h2d_plan_layout.argtypes = [vp]
             lib.h2d_plan_layout.restype = C.c_int32
+            lib.h2d_plan_seed_colbuf.argtypes = [vp, C.c_int, vp]
             lib.h2d_plan_create.argtypes = [P(PlanDesc)]
             lib.h2d_plan_create.restype = vp
             lib.h2d_plan_destroy.argtypes = [vp]

@@ -25,6 +25,7 @@ from ..parallel.decomp import Decomposition, OPPOSITE, TileSpec
 from ..utils.timing import nvtx_range
 
 COL_MARGIN = 32  # floats; keeps owned column 0 128-byte aligned and >= roundup4(KMAX)
+COL_PACK = 8     # floats per row of a packed column-ghost buffer (TK_CW)
 
 
 def _round_up(v: int, m: int) -> int:
@@ -73,7 +74,7 @@ class TileField:
     """
 
     def __init__(self, spec: TileSpec, nx: int, ny: int, halo: int, device,
-                 storage: Optional[List[torch.Tensor]] = None):
+                 storage: Optional[List[torch.Tensor]] = None, colbuf=None):
         self.spec = spec
         self.tile = padded_geometry(spec, nx, ny, halo)
         self.device = torch.device(device)
@@ -84,6 +85,11 @@ class TileField:
             self.buf = storage
             for b in self.buf:
                 assert tuple(b.shape) == shape and b.dtype == torch.float32 and b.is_contiguous()
+        # packed column-ghost buffers [side W/E][parity], rows x 8 floats each (csrc/tk_task.cuh):
+        # the W / E neighbours write their edge columns here as one contiguous stream
+        self.colbuf = colbuf if colbuf is not None else [
+            [torch.zeros((spec.rows, COL_PACK), dtype=torch.float32, device=self.device) for _ in range(2)]
+            for _ in range(2)]
 
     def owned(self, parity: int) -> torch.Tensor:
         t = self.tile
@@ -154,7 +160,9 @@ class TileEngine:
         f = self.field
         self.plan = K.Plan(f.tile, self.phys, f.buf[0].data_ptr(), f.buf[1].data_ptr(), self.kmax,
                            self.chunk_rows, peers=peers, flags_in_ptr=self.flags_in.data_ptr(),
-                           spin_timeout_s=self.spin_timeout_s, device=f.device, layout=self.layout)
+                           spin_timeout_s=self.spin_timeout_s, device=f.device, layout=self.layout,
+                           colbuf_in=[[f.colbuf[side][par].data_ptr() if peers.get(d) is not None else 0
+                                       for par in (0, 1)] for side, d in ((0, "W"), (1, "E"))])
         self.vals_ptrs = torch.tensor(all_vals_ptrs, dtype=torch.int64, device=f.device)
         self.flags_ptrs = torch.tensor(all_nflags_ptrs, dtype=torch.int64, device=f.device)
         self._fault = tensor_from_ptr(self.plan.fault_ptr, (1,), torch.int32, f.device)
@@ -261,9 +269,13 @@ class Heat2DSolver:
                 # I publish my epoch into the slot of the neighbour's flags_in that
                 # is indexed by the direction I am in as seen from there.
                 slot = N.DIRS.index(OPPOSITE[d])
+                # my W band lands in the west neighbour's EAST packed buffer and vice versa
+                side = {"W": 1, "E": 0}.get(d)
+                cb = [nf.colbuf[side][par].data_ptr() for par in (0, 1)] if side is not None else [0, 0]
                 peers[d] = K.PeerRef(nf.buf[0].data_ptr(), nf.buf[1].data_ptr(),
                                      self.engines[nb].flags_in.data_ptr() + 4 * slot,
-                                     nf.tile.x0, nf.tile.y0, nf.tile.halo_r, nf.tile.halo_c, nf.tile.pitch)
+                                     nf.tile.x0, nf.tile.y0, nf.tile.halo_r, nf.tile.halo_c, nf.tile.pitch,
+                                     cb[0], cb[1])
             e.build(peers if w > 1 else {}, all_vals, all_nfl)
 
     # ------------------------------------------------------------- initialise
@@ -276,7 +288,19 @@ class Heat2DSolver:
             K.init_field(f.buf[0], f.tile, mode, True)
         self.parity = 0
         self.steps_done = self.cfg.start_step
+        self._seed_colbufs()
         return self
+
+    def seed_colbufs(self):
+        """Call after writing a padded array (`fields[i].buf[parity]`) directly."""
+        self._seed_colbufs()
+
+    def _seed_colbufs(self):
+        """The padded arrays were just filled by something other than the neighbours' launches:
+        bring the packed column-ghost buffers of the current parity in line with the margins."""
+        for e in self.engines:
+            if e.plan is not None:
+                e.plan.seed_colbuf(self.parity)
 
     def load(self, grid, parity: int = 0):
         """Scatter a full nx x ny grid (host or device tensor / ndarray) to the tiles."""
@@ -287,6 +311,7 @@ class Heat2DSolver:
             f.buf[1 - parity].zero_()
             f.load_from_global(grid, parity)
         self.parity = parity
+        self._seed_colbufs()
         return self
 
     # -------------------------------------------------------------------- run

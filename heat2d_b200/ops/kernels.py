@@ -154,9 +154,11 @@ class PeerRef:
     """What a plan needs to know about one neighbour (all raw device addresses)."""
 
     def __init__(self, buf0: int, buf1: int, flag: int, x0: int, y0: int, halo_r: int, halo_c: int,
-                 pitch: int):
+                 pitch: int, colbuf0: int = 0, colbuf1: int = 0):
         self.buf0, self.buf1, self.flag = int(buf0), int(buf1), int(flag)
         self.x0, self.y0, self.halo_r, self.halo_c, self.pitch = x0, y0, halo_r, halo_c, int(pitch)
+        # W / E neighbours: their packed column-ghost buffers (parity 0 / 1) facing this tile
+        self.colbuf0, self.colbuf1 = int(colbuf0), int(colbuf1)
 
 
 class Plan:
@@ -164,7 +166,8 @@ class Plan:
 
     def __init__(self, tile: N.Tile, phys: N.Phys, buf0_ptr: int, buf1_ptr: int, kmax: int,
                  chunk_rows: int = 0, peers: Optional[dict] = None, flags_in_ptr: int = 0,
-                 scratch_ptr: int = 0, spin_timeout_s: float = 10.0, device=None, layout: int = 0):
+                 scratch_ptr: int = 0, spin_timeout_s: float = 10.0, device=None, layout: int = 0,
+                 colbuf_in=None):
         self._lib = N.cuda()
         self.tile, self.phys, self.kmax = tile, phys, kmax
         self.device = device
@@ -184,10 +187,16 @@ class Plan:
                 e.buf[1] = p.buf1
                 e.flag = p.flag
                 e.x0, e.y0, e.halo_r, e.halo_c, e.pitch = p.x0, p.y0, p.halo_r, p.halo_c, p.pitch
+                e.colbuf[0] = p.colbuf0 or None
+                e.colbuf[1] = p.colbuf1 or None
         d.flags_in = flags_in_ptr or None
         d.scratch = scratch_ptr or None
         d.spin_timeout_ns = int(spin_timeout_s * 1e9)
         d.layout = int(layout)
+        if colbuf_in is not None:      # [[west parity 0, west parity 1], [east parity 0, east parity 1]]
+            for side in (0, 1):
+                for par in (0, 1):
+                    d.colbuf_in[side][par] = int(colbuf_in[side][par]) or None
         self._desc = d
         with torch.cuda.device(device):
             h = self._lib.h2d_plan_create(C.byref(d))
@@ -298,6 +307,12 @@ class Plan:
                 int(steps), int(k), int(block_rows), int(skew_rows), int(wave_rows), epoch0 & 0xFFFFFFFF,
                 _stream_ptr(self.device), C.byref(par), C.byref(used)))
         return par.value, int(used.value)
+
+    def seed_colbuf(self, parity: int):
+        """After the padded array of `parity` was filled by anything but the neighbours' launches
+        (initial condition, load, upload): copy its ghost columns into the packed buffers."""
+        with torch.cuda.device(self.device):
+            N.check(self._lib, self._lib.h2d_plan_seed_colbuf(self._h, int(parity), _stream_ptr(self.device)))
 
     @property
     def launch_count(self) -> int:

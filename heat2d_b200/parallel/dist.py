@@ -31,7 +31,7 @@ import torch.distributed as dist
 
 from .. import _native as N
 from ..config import HeatConfig
-from ..models.heat import (Heat2DSolver, RunResult, TileEngine, TileField, _layout_code, padded_bytes,
+from ..models.heat import (COL_PACK, Heat2DSolver, RunResult, TileEngine, TileField, _layout_code, padded_bytes,
                            padded_geometry, tensor_from_ptr)
 from ..ops import kernels as K
 from .decomp import DIRS, Decomposition, OPPOSITE
@@ -77,7 +77,11 @@ class PeerArena:
         self.off_flags = self.off_buf[1] + _align(pb)
         self.off_vals = self.off_flags + 512
         self.off_nflags = self.off_vals + _align(2 * world * 4)
-        self.bytes = self.off_nflags + _align(2 * world * 4)
+        # packed column-ghost buffers [side][parity], rows x 8 floats each
+        cb = _align(tile.rows * COL_PACK * 4)
+        base = self.off_nflags + _align(2 * world * 4)
+        self.off_colbuf = [[base + (2 * side + par) * cb for par in (0, 1)] for side in (0, 1)]
+        self.bytes = base + 4 * cb
         self.handle = self.lib.h2d_arena_create(self.bytes)
         if not self.handle:
             raise N.NativeError(-5, N.last_error(self.lib))
@@ -98,7 +102,7 @@ class PeerArena:
 
     def meta(self) -> dict:
         return {"off_buf": self.off_buf, "off_flags": self.off_flags, "off_vals": self.off_vals,
-                "off_nflags": self.off_nflags}
+                "off_nflags": self.off_nflags, "off_colbuf": self.off_colbuf}
 
     def close(self):
         for p in self.peers.values():
@@ -135,7 +139,9 @@ class DistributedHeat2DSolver(Heat2DSolver):
         a = self.arena
         shape = (spec.rows + 2 * cfg.halo, tile.pitch)
         bufs = [tensor_from_ptr(a.ptr + a.off_buf[p], shape, torch.float32, dev, owner=a) for p in (0, 1)]
-        f = TileField(spec, cfg.nx, cfg.ny, cfg.halo, dev, storage=bufs)
+        colbuf = [[tensor_from_ptr(a.ptr + a.off_colbuf[side][p], (spec.rows, COL_PACK), torch.float32, dev, owner=a)
+                   for p in (0, 1)] for side in (0, 1)]
+        f = TileField(spec, cfg.nx, cfg.ny, cfg.halo, dev, storage=bufs, colbuf=colbuf)
         self.fields = [f]
         flags_in = tensor_from_ptr(a.ptr + a.off_flags, (64,), torch.int32, dev, owner=a)
         vals = tensor_from_ptr(a.ptr + a.off_vals, (2 * w,), torch.float32, dev, owner=a)
@@ -164,9 +170,12 @@ class DistributedHeat2DSolver(Heat2DSolver):
             m = metas[nb]
             nt = dict(zip([n for n, _ in N.Tile._fields_], m["tile"]))
             slot = DIRS.index(OPPOSITE[d])
+            # my W band lands in the west neighbour's EAST packed buffer and vice versa
+            side = {"W": 1, "E": 0}.get(d)
+            cb = [base[nb] + m["off_colbuf"][side][p] for p in (0, 1)] if side is not None else [0, 0]
             peers[d] = K.PeerRef(base[nb] + m["off_buf"][0], base[nb] + m["off_buf"][1],
                                  base[nb] + m["off_flags"] + 4 * slot, nt["x0"], nt["y0"], nt["halo_r"],
-                                 nt["halo_c"], nt["pitch"])
+                                 nt["halo_c"], nt["pitch"], cb[0], cb[1])
         all_vals = [base[q] + metas[q]["off_vals"] for q in range(w)]
         all_nfl = [base[q] + metas[q]["off_nflags"] for q in range(w)]
         eng.build(peers if w > 1 else {}, all_vals, all_nfl)
@@ -193,6 +202,7 @@ class DistributedHeat2DSolver(Heat2DSolver):
         f = self.fields[0]
         f.buf[parity].copy_(padded_host, non_blocking=True)
         self.parity = parity
+        self._seed_colbufs()
         self.barrier()
         return self
 

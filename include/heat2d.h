@@ -174,6 +174,11 @@ typedef struct h2d_peer {
   int32_t x0, y0;           /* neighbour tile origin (global)                     */
   int32_t halo_r, halo_c;
   int64_t pitch;
+  /* W / E entries only, optional: the neighbour's PACKED column-ghost buffers (parity 0 / 1)
+   * that this rank's edge columns go into — the neighbour's h2d_plan_desc_t::colbuf_in of
+   * the facing side.  NULL: the columns are stored in place into buf[] (slow on long tiles:
+   * one short remote write per row).                                                      */
+  float* colbuf[2];
 } h2d_peer_t;
 
 typedef struct h2d_plan_desc {
@@ -194,6 +199,14 @@ typedef struct h2d_plan_desc {
    * 256-column strips).  Strict arithmetic always uses v4.  Results are bit-identical. */
   int32_t layout;
   int32_t reserved;
+  /* Packed column-ghost buffers of THIS rank, [side][parity] (side 0 = ghosts west of the
+   * tile, 1 = east), each rows x 8 floats, in memory the W / E neighbour can reach (it gets
+   * the pointers as its h2d_peer_t::colbuf).  The neighbour writes its k edge columns of tile
+   * row r to floats [8r, 8r + k); this rank's edge tasks copy the rows they read into the
+   * margins of the source array first.  After filling a padded array from the host
+   * (initial condition, restart, upload) call h2d_plan_seed_colbuf for that parity.  All NULL:
+   * ghost columns arrive in place.                                                        */
+  float* colbuf_in[2][2];
 } h2d_plan_desc_t;
 
 size_t h2d_plan_scratch_bytes(const h2d_tile_t* tile, int32_t kmax, int32_t chunk_rows);
@@ -205,6 +218,10 @@ int32_t h2d_plan_chunk_rows(const h2d_tile_t* tile, int32_t kmax, int32_t with_p
 int32_t h2d_plan_chunk_rows_ex(const h2d_tile_t* tile, int32_t kmax, int32_t with_peers, int32_t arith,
                                int32_t layout);
 int32_t h2d_plan_strip_width(int32_t arith, int32_t layout);
+/* Copy the ghost columns found in the margins of buf[parity] (rows 0 .. rows-1) into this
+ * rank's packed column-ghost buffers of that parity: to be called after the padded array was
+ * filled by anything but the neighbours' launches.  No-op without colbuf_in.               */
+int h2d_plan_seed_colbuf(h2d_plan_t* plan, int parity, void* stream);
 /* Lane layout a plan was built with (1 = v4, 2 = ab2, 3 = ab4). */
 int32_t h2d_plan_layout(const h2d_plan_t* plan);
 h2d_plan_t* h2d_plan_create(const h2d_plan_desc_t* desc);
