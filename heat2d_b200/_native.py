@@ -34,7 +34,6 @@ class Tile(C.Structure):
         ("rows", C.c_int32), ("cols", C.c_int32),
         ("halo_r", C.c_int32), ("halo_c", C.c_int32),
         ("pitch", C.c_int64),
-        ("colbuf", C.c_void_p * 2),
     ]
 
 
