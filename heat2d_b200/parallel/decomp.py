@@ -109,18 +109,16 @@ class Decomposition:
 
     @staticmethod
     def auto(nx: int, ny: int, world: int, min_rows: int = 512) -> "Decomposition":
-        """Process grid for `world` GPUs of one NVSwitch box.
+        """Process grid for `world` GPUs of one NVSwitch box: the 2-D block decomposition of
+        the reference (GRIDX x GRIDY, grad1612_mpi_heat.c:47-52) with the most square tiles,
+        i.e. the least halo volume, preferring to split rows when two grids tie (a row
+        band is contiguous in memory).
 
-        Row strips (px = world, py = 1) whenever every strip keeps at least
-        `min_rows` rows: a row halo is whole contiguous rows (full 128-byte NVLink
-        packets, 8 row-steps per launch), while a column halo is 32 bytes per row on
-        EVERY row step — measured on 2 B200: 32768^2 as 2x1 8052 GLUP/s, as 1x2
-        6770 GLUP/s (8145 with the column stores disabled).  With every GPU pair at
-        full bandwidth the larger surface of strips costs nothing.  Otherwise the
-        most square grid, preferring to split rows.
-        """
-        if world <= nx and nx // world >= min_rows:
-            return Decomposition(nx, ny, world, 1)
+        With the column bands travelling through packed ghost buffers every layout runs at
+        the same speed on B200 (32768^2, fp32: 4x1 16484, 2x2 16478, 1x4 16242 GLUP/s on four
+        GPUs; 1x2 = 2x1 = 8583 on two), so the choice is about halo bytes and tile shape
+        only.  Tiles keep at least `min_rows` rows and columns where the grid allows it
+        (short tiles are all pipeline fill)."""
         best = None
         for px in range(1, world + 1):
             if world % px:
@@ -128,8 +126,9 @@ class Decomposition:
             py = world // px
             if px > nx or py > ny:
                 continue
-            cost = nx / px + ny / py  # halo volume per tile
-            key = (cost, -px)
+            thin = (nx // px < min_rows) + (ny // py < min_rows)   # avoid tiles that are too short / narrow
+            cost = nx / px + ny / py                               # halo volume per tile
+            key = (thin, cost, -px)
             if best is None or key < best[0]:
                 best = (key, px, py)
         if best is None:

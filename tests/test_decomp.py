@@ -59,7 +59,11 @@ def test_strips_and_auto():
     assert [(t.x0, t.rows) for t in d.tiles] == [(0, 214), (214, 213), (427, 213)]
     assert all(t.cols == 640 for t in d.tiles)
     a = Decomposition.auto(32768, 32768, 8)
-    assert (a.px, a.py) == (8, 1)          # row strips on an NVSwitch box
-    b = Decomposition.auto(640, 65536, 8)  # too few rows for 8 strips of >= 512
-    assert b.px * b.py == 8 and b.py > 1
+    assert (a.px, a.py) == (4, 2)          # most square blocks, rows split first on a tie
+    assert (Decomposition.auto(32768, 32768, 4).px, Decomposition.auto(32768, 32768, 4).py) == (2, 2)
+    assert (Decomposition.auto(32768, 32768, 2).px, Decomposition.auto(32768, 32768, 2).py) == (2, 1)
+    b = Decomposition.auto(640, 65536, 8)  # too few rows to split: column strips
+    assert (b.px, b.py) == (1, 8)
+    c = Decomposition.auto(65536, 640, 8)
+    assert (c.px, c.py) == (8, 1)
     assert Decomposition.auto(100, 100, 1).world == 1

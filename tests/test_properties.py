@@ -66,8 +66,12 @@ def test_auto_decomposition_uses_every_gpu(nx, ny, world):
         assert all(px > nx or world // px > ny for px in range(1, world + 1) if world % px == 0)
         return
     assert d.world == world
-    if nx // world >= 512:
-        assert (d.px, d.py) == (world, 1)   # row strips inside one NVSwitch box
+    # no other fitting grid has fewer thin tiles, nor (equally thin) less halo per tile
+    def key(px):
+        py = world // px
+        return ((nx // px < 512) + (ny // py < 512), nx / px + ny / py)
+    fits = [px for px in range(1, world + 1) if world % px == 0 and px <= nx and world // px <= ny]
+    assert key(d.px) == min(key(px) for px in fits)
 
 
 @given(st.integers(0, 3000), st.integers(1, KMAX), st.booleans(), st.integers(1, 64), st.integers(0, 500))
