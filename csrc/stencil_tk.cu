@@ -98,10 +98,7 @@ static int sm_count() {
 }
 
 // Resident warps per SM of the kernels of one plan (TkBounds in tk_kernel.cuh).
-static int warps_per_sm(int kmax, int lay) {
-  if (lay == LAY_AB4) return kmax <= 4 ? 12 : 8;
-  return kmax <= 5 ? 16 : 12;
-}
+static int warps_per_sm(int kmax, int lay) { return tk_min_blocks(kmax, lay) * TK_WARPS; }
 
 // Lane layout of the fp32 kernels.  Default: H2D_FP32_LAYOUT=v4|ab2|ab4, else the measured
 // best.  Strict modes always use V4 (their arithmetic is scalar).
@@ -902,6 +899,7 @@ int h2d_plan_solve_pipelined_many(h2d_plan_t* const* plans, int n_plans, const f
 
 int64_t h2d_plan_launch_count(const h2d_plan_t* p) { return p ? p->launches : 0; }
 uint32_t* h2d_plan_strict_fallback_ptr(h2d_plan_t* p) { return p ? (uint32_t*)p->scratch + 12 : nullptr; }
+uint32_t* h2d_plan_team_fallback_ptr(h2d_plan_t* p) { return p ? (uint32_t*)p->scratch + 15 : nullptr; }
 float* h2d_plan_norm_ptr(h2d_plan_t* p) { return p ? (float*)((unsigned*)p->scratch + 2) : nullptr; }
 uint32_t* h2d_plan_fault_ptr(h2d_plan_t* p) { return p ? (uint32_t*)p->scratch + 3 : nullptr; }
 uint64_t* h2d_plan_stats_ptr(h2d_plan_t* p) { return p ? (uint64_t*)((uint32_t*)p->scratch + 8) : nullptr; }

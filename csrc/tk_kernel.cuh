@@ -9,16 +9,25 @@
 
 namespace h2d {
 
+// Resident CTAs per SM the kernels are compiled for (__launch_bounds__), also used by the
+// host to size tasks (stencil_tk.cu: warps_per_sm).
+// V4 / AB2 (12 state registers per level): K <= 5 fits 128 registers (4 CTAs = 16 warps
+// per SM); deeper pipelines get 168 registers (3 CTAs = 12 warps) instead of spilling.
+// Measured on B200 at K = 8, V4: 12 warps / 166 regs / no spills 4.43 TLUP/s; 13-14 warps
+// with __maxnreg__ 152 / 144 (32-72 B of spills) 4.31 TLUP/s; 16 warps at 128 registers
+// (244 B of spills) 3.9 TLUP/s.
+// AB4 (24 state registers per level): 2 CTAs = 8 warps per SM at K >= 5 (shared memory
+// allows no more either: 112 KB per CTA), 3 below.
+__host__ __device__ constexpr int tk_min_blocks(int k, int lay) {
+#ifdef H2D_TK_MINBLOCKS
+  return H2D_TK_MINBLOCKS;   // experiments only
+#else
+  return lay == LAY_AB4 ? ((k <= 4) ? 3 : 2) : ((k <= 5) ? 4 : 3);
+#endif
+}
 template <int K, int LAY>
 struct TkBounds {
-  // V4 / AB2 (12 state registers per level): K <= 5 fits 128 registers (4 CTAs = 16 warps
-  // per SM); deeper pipelines get 168 registers (3 CTAs = 12 warps) instead of spilling.
-  // Measured on B200 at K = 8, V4: 12 warps / 166 regs / no spills 4.43 TLUP/s; 13-14 warps
-  // with __maxnreg__ 152 / 144 (32-72 B of spills) 4.31 TLUP/s; 16 warps at 128 registers
-  // (244 B of spills) 3.9 TLUP/s.
-  // AB4 (24 state registers per level): 2 CTAs = 8 warps per SM at K >= 5 (shared memory
-  // allows no more either: 112 KB per CTA), 3 below.
-  static constexpr int min_blocks = LAY == LAY_AB4 ? ((K <= 4) ? 3 : 2) : ((K <= 5) ? 4 : 3);
+  static constexpr int min_blocks = tk_min_blocks(K, LAY);
 };
 
 // XTR = false: a launch with neither peers nor a convergence norm (the common single-GPU

@@ -41,7 +41,8 @@ namespace h2d {
 inline int round_up4(int k) { return (k + 3) & ~3; }
 
 // Scratch header (256 bytes, 32-bit words): 0 edge counter, 1 done counter, 2 norm value,
-// 3 fault word, 8-11 two 64-bit wait statistics, 12-14 strict-mode fallback counters.
+// 3 fault word, 8-11 two 64-bit wait statistics, 12-14 strict-mode fallback counters,
+// 15 strips of cluster launches (stencil_team.cu) whose data left the fast strict evaluation.
 inline void tk_fill_scratch_ptrs(TkArgs& a, void* scratch) {
   unsigned* hdr = (unsigned*)scratch;
   a.edge_counter = hdr + 0;

@@ -138,6 +138,10 @@ def cuda():
             lib.h2d_plan_wave_rows.restype = C.c_int32
             lib.h2d_plan_run_dataflow.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
             lib.h2d_plan_run_dataflow.restype = C.c_int
+            lib.h2d_plan_launch_team.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+            lib.h2d_plan_launch_team.restype = C.c_int
+            lib.h2d_plan_team_fallback_ptr.argtypes = [C.c_void_p]
+            lib.h2d_plan_team_fallback_ptr.restype = C.c_void_p
             lib.h2d_plan_chunk_rows.argtypes = [P(Tile), C.c_int32, C.c_int32]
             lib.h2d_plan_chunk_rows.restype = C.c_int32
             lib.h2d_plan_chunk_rows_ex.argtypes = [P(Tile), C.c_int32, C.c_int32, C.c_int32, C.c_int32]

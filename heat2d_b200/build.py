@@ -29,7 +29,7 @@ LIB = Path(__file__).resolve().parent / "_lib"
 OBJ = LIB / "obj"
 
 CPU_SOURCES = ["oracle.cpp", "dump.cpp"]
-CUDA_SOURCES = ["basic_kernels.cu", "stencil_tk.cu", "stencil_flow.cu", "resident.cu", "peer.cu"]
+CUDA_SOURCES = ["basic_kernels.cu", "stencil_tk.cu", "stencil_flow.cu", "stencil_team.cu", "resident.cu", "peer.cu"]
 # tk_inst.cu is compiled once per (arithmetic, lane layout, extras) combination:
 # (object name, ARITH, LAY, XTR).  ARITH 0 fp32 / 1 strict / 2 strict-fma (heat2d.h);
 # LAY 0 v4 / 1 ab2 / 2 ab4 (csrc/tk_task.cuh); strict arithmetic exists in the v4 layout only.

@@ -237,6 +237,20 @@ class Plan:
                                                                  _stream_ptr(self.device)))
         return src_parity ^ (n_epochs & 1)
 
+    def launch_team(self, src_parity: int, k: int, cluster: int = 2, chunk_rows: int = 0) -> int:
+        """One k-step sweep (5 <= k <= 8) as a cluster launch: teams of 4 * cluster adjacent strips
+        that share their edge columns through (distributed) shared memory (h2d_plan_launch_team).
+        Returns the parity of the buffer that holds the result."""
+        with torch.cuda.device(self.device):
+            N.check(self._lib, self._lib.h2d_plan_launch_team(self._h, src_parity, k, cluster, chunk_rows,
+                                                                _stream_ptr(self.device)))
+        return src_parity ^ 1
+
+    @property
+    def team_fallback_ptr(self) -> int:
+        """Device address of the counter of team strips whose data left the fast strict evaluation."""
+        return int(self._lib.h2d_plan_team_fallback_ptr(self._h))
+
     def solve_pipelined(self, host_in: torch.Tensor, host_out: torch.Tensor, steps: int, k: int,
                         block_rows: int = 0, skew_rows: int = 0) -> int:
         """Upload `host_in`, advance `steps` steps, download into `host_out`, overlapped

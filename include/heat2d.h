@@ -266,6 +266,20 @@ int h2d_plan_run_many(h2d_plan_t* const* plans, int n_plans, int src_parity, int
  * The reference launches once per time step (grad1612_cuda_heat.cu:82-85).          */
 int h2d_plan_run_dataflow(h2d_plan_t* plan, int src_parity, int k, int n_epochs, void* stream);
 
+/* One k-step sweep (5 <= k <= 8) as a CLUSTER launch: the tile is cut into teams of
+ * 4 * cluster adjacent strips (cluster = 1, 2 or 4 CTAs), one team per thread-block cluster;
+ * the strips of a team advance in row lock-step and hand each other their edge columns
+ * half-way through the k levels — through shared memory inside a CTA, through distributed
+ * shared memory between the CTAs — so that adjacent strips overlap by 8 columns instead of
+ * 16 (csrc/tk_team.cuh).  Single-tile plans, v4 lane layout, fp32 and strict-fma arithmetic,
+ * no norm.  chunk_rows = 0 picks the task height.  Same result, bit for bit, as
+ * h2d_plan_launch; in strict-fma, data outside the domain of the fast evaluation is COUNTED
+ * (h2d_plan_team_fallback_ptr) instead of re-evaluated: repeat the sweep with h2d_plan_launch
+ * if the counter moved.  The reference has one thread per point and no reuse
+ * (grad1612_cuda_heat.cu:55-62).                                                     */
+int h2d_plan_launch_team(h2d_plan_t* plan, int src_parity, int k, int cluster, int chunk_rows, void* stream);
+uint32_t* h2d_plan_team_fallback_ptr(h2d_plan_t* plan);
+
 /* Upload, solve, download — overlapped.  For a single-tile plan: copies the nx x ny
  * field `host_in` (pinned host memory, `in_pitch` floats per row) into buf[0], advances
  * it `steps` steps in launches of k, and copies the result to `host_out`, with the
