@@ -418,6 +418,23 @@ def main(argv=None):
                  "gpu_launches": l2, "clocks": c2,
                  "roofline": _roofline(g2, nx, ny, px, py, k, a.chunk_rows) if other == "fp32" else None}
         getattr(s2, "close", lambda: None)()
+        del s2
+        torch.cuda.empty_cache()
+
+    team = None
+    if world == 1 and backend == "fused" and not a.no_extra and a.arith != "fp32" and k >= 5 and not a.conv:
+        # opt-in launch mode (--team on / HeatConfig.team): the strips of a CTA share their edge
+        # columns through shared memory instead of recomputing them; same bits (verified in
+        # tests/test_gpu_team.py).  Not the default — it pays off only on tiles this large — so it
+        # is reported next to the headline, not as the headline.
+        s3 = _make_solver(cfg.replace(team="on"), world, device, backend).initialize()
+        r3, l3, _ = _time_run(s3, a.steps, a.warmup, world, device, local)
+        team = {"arith": a.arith, "value": nx * ny * a.steps / r3.elapsed_s / 1e9, "unit": "GLUP/s",
+                "ms_per_step": r3.elapsed_s / a.steps * 1e3, "gpu_launches": l3,
+                "what": "the same run with HeatConfig.team='on' (cluster launches, csrc/tk_team.cuh)"}
+        getattr(s3, "close", lambda: None)()
+        del s3
+        torch.cuda.empty_cache()
 
     if rank == 0:
         dtype = {"fp32": "fp32", "strict-fma": "fp32 storage, fp64 intermediates (bit-identical to the nvcc-built "
@@ -450,6 +467,8 @@ def main(argv=None):
             # the same-arithmetic number under its own name as well, whatever the headline is
             out["same_arith"] = {"arith": a.arith, "value": glups, "unit": "GLUP/s",
                                  "ms_per_step": secs / a.steps * 1e3}
+        if team is not None:
+            out["team_mode"] = team
         if e2e is not None:
             out["e2e"] = e2e
         print(json.dumps(out), flush=True)

@@ -26,9 +26,13 @@ tk_team_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
   constexpr bool STRICT = ARITH != H2D_ARITH_FP32;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t ring = smem_u32(smem) + warp * (TK_STAGES * TEAM_STAGE_BYTES);
+  // ring | mbarriers | exchange area, the latter aligned to its size (the launch reserves the slack)
   const uint32_t bars = smem_u32(smem) + TEAM_SMEM_RING + warp * TK_STAGES * 8;
-  const uint32_t xch = smem_u32(smem) + TEAM_SMEM_RING + TK_SMEM_BARS;
+  const uint32_t xch = (smem_u32(smem) + TEAM_SMEM_RING + TK_SMEM_BARS + TEAM_XBYTES - 1) & ~(uint32_t)(TEAM_XBYTES - 1);
   constexpr int cs = CS;
+  // device-side run control and the fault word, as in tk_kernel: the whole grid takes the same exit
+  if (a.ctl != nullptr && *reinterpret_cast<const volatile uint32_t*>(a.ctl) != a.run_if) return;
+  if (*reinterpret_cast<const volatile uint32_t*>(a.fault) != 0u) return;
   const int cr = CS > 1 ? (int)cluster_ctarank() : 0;
 
   // exchange area: zero (the first row step reads it), then the arrive the first wait pairs with
@@ -78,12 +82,20 @@ tk_team_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
   } else {
     run_task_team<K, ARITH, IMM, false, STRICT, CS>(&tmap, a, dst, tc, r_lo, r_hi, ring, bars, lane, track);
   }
-  if (STRICT) {
-    // Data outside the fast evaluation's domain: count the strip (scratch header word 15,
-    // h2d_plan_team_fallback_ptr); the caller repeats the sweep with h2d_plan_launch, whose
-    // kernels fall back task by task.
-    track = __reduce_max_sync(0xffffffffu, track);
-    if (lane == 0 && track >= STRICT_FAST_LIMIT) atomicAdd(a.strict_fb + 3, 1u);   // header word 15
+  if constexpr (STRICT) {
+    // Data outside the domain of the fast evaluation (negative, non-finite, huge) anywhere in
+    // the team: a one-CTA team runs the task again with the plain evaluation — all four warps,
+    // they work in lock-step — and overwrites every store of the first run.  Larger clusters
+    // only count the strips (scratch header word 15, h2d_plan_team_fallback_ptr): their caller
+    // repeats the sweep with h2d_plan_launch, whose kernels fall back task by task.
+    const bool bad = __any_sync(0xffffffffu, track >= STRICT_FAST_LIMIT);
+    if (bad && lane == 0) atomicAdd(a.strict_fb + 3, 1u);   // header word 15
+    if (CS == 1) {
+      if (__syncthreads_or(bad ? 1 : 0)) {
+        const int box0 = (r_hi - r_lo + 2 * K + 1 + TK_BR - 1) / TK_BR;
+        run_task_team<K, ARITH, false, true, false, CS>(&tmap, a, dst, tc, r_lo, r_hi, ring, bars, lane, track, box0);
+      }
+    }
   }
 }
 
@@ -105,6 +117,7 @@ static tk_team_fn_t team_pick_cs(int k, int arith, bool imm) {
     case H2D_ARITH_FP32:
       return imm ? team_pick_k<H2D_ARITH_FP32, true, CS>(k) : team_pick_k<H2D_ARITH_FP32, false, CS>(k);
     case H2D_ARITH_STRICT_FMA: return team_pick_k<H2D_ARITH_STRICT_FMA, false, CS>(k);
+    case H2D_ARITH_STRICT: return CS == 1 ? team_pick_k<H2D_ARITH_STRICT, false, 1>(k) : nullptr;
     default: return nullptr;
   }
 }
@@ -123,7 +136,22 @@ using namespace h2d;
 
 extern "C" {
 
+int h2d_plan_launch_team_ex(h2d_plan_t* p, int src_parity, int k, int cluster, int chunk_rows,
+                            const uint32_t* ctl, uint32_t run_if, void* stream);
+
 int h2d_plan_launch_team(h2d_plan_t* p, int src_parity, int k, int cluster, int chunk_rows, void* stream) {
+  return h2d_plan_launch_team_ex(p, src_parity, k, cluster, chunk_rows, nullptr, 0u, stream);
+}
+
+int h2d_plan_team_eligible(const h2d_plan_t* p, int k, int cluster) {
+  if (!p || p->has_peers || p->lay != LAY_V4 || k < 5 || k > p->desc.kmax || k > TK_KMAX) return 0;
+  if (p->desc.phys.arith != H2D_ARITH_FP32 && p->desc.phys.arith != H2D_ARITH_STRICT_FMA &&
+      p->desc.phys.arith != H2D_ARITH_STRICT) return 0;
+  return p->desc.tile.cols >= team_cols(cluster * TK_WARPS, round_up4(k));
+}
+
+int h2d_plan_launch_team_ex(h2d_plan_t* p, int src_parity, int k, int cluster, int chunk_rows,
+                            const uint32_t* ctl, uint32_t run_if, void* stream) {
   if (!p) return h2d_fail(H2D_EINVAL, "h2d_plan_launch_team: null plan");
   if (src_parity != 0 && src_parity != 1) return h2d_fail(H2D_EINVAL, "h2d_plan_launch_team: bad parity");
   if (k < 5 || k > p->desc.kmax || k > TK_KMAX)
@@ -160,7 +188,10 @@ int h2d_plan_launch_team(h2d_plan_t* p, int src_parity, int k, int cluster, int 
       const int r = (t.rows + c - 1) / c;
       if (r < 8 && c > 1) break;
       const double waves = ceil((double)((t.rows + r - 1) / r) * ta.n_teams / slots);
-      const double cost = (waves + 0.25) * (double)(r + 2 * k + 9);
+      // (+0.5, not the +0.25 of independent strips: a team is as slow as its slowest strip, and
+      // the strips on the global boundary run the select-heavy body; 16384^2 strict-fma:
+      // 432-row tasks in 3 waves 1209 GLUP/s, 261-row tasks in 5 waves 1296)
+      const double cost = (waves + 0.5) * (double)(r + 2 * k + 9);
       if (cost < best * (1.0 - 1e-9)) { best = cost; R = r; }
     }
   }
@@ -179,12 +210,15 @@ int h2d_plan_launch_team(h2d_plan_t* p, int src_parity, int k, int cluster, int 
   a.fw = p->fw;
   tk_fill_scratch_ptrs(a, p->scratch);
   a.timeout_ns = p->desc.spin_timeout_ns > 0 ? p->desc.spin_timeout_ns : 10000000000LL;
+  a.ctl = ctl;
+  a.run_if = run_if;
 
   const int smem = tk_team_smem_bytes();
   H2D_CUDA_TRY(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   fn<<<(unsigned)(ta.n_teams * ta.n_chunks * cluster), TK_WARPS * 32, (size_t)smem, cs>>>(p->tmap[src_parity], a, ta);
   H2D_CHECK_LAUNCH("tk_team_kernel");
   p->launches++;
+  p->seq++;
   return H2D_OK;
 }
 

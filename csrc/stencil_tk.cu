@@ -471,6 +471,10 @@ int h2d_plan_launch_ex(h2d_plan_t* p, int src_parity, int k, uint32_t epoch, int
 #else
   const bool xtr = p->has_peers || norm != H2D_NORM_NONE;
 #endif
+  // h2d_plan_desc_t::team: sweeps without neighbours and without a norm go out as cluster
+  // launches whose strips share their edge columns (stencil_team.cu) where the tile allows it
+  if (p->desc.team != 0 && !xtr && h2d_plan_team_eligible(p, k, 1))
+    return h2d_plan_launch_team_ex(p, src_parity, k, 1, 0, ctl, run_if, stream);
   const bool imm = coef_is_reference(p->geo, p->desc.phys.arith);
   tk_fn_t fn = tk_pick(k, p->desc.phys.arith, p->lay, imm, xtr);
   if (!fn) return h2d_fail(H2D_EINVAL, "h2d_plan_launch: no kernel for k = %d", k);

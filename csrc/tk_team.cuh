@@ -26,8 +26,7 @@
 // step.  Ordering instead rests on (a) the arrive being issued after the first instruction that
 // consumes the row just read, i.e. after the read has returned — nobody overwrites a row that
 // is still being read —
-// and (b) a warp's shared-memory store preceding its arrive in program order, hundreds of
-// cycles before any warp that waited for that arrive can have a load reach the same SM.
+// and (b) a CTA-scope fence between a warp's shared-memory store and its arrive.
 #pragma once
 #include "tk_task.cuh"
 
@@ -36,13 +35,17 @@ namespace h2d {
 constexpr int TEAM_STRIDE = Lay<LAY_V4>::W - 8;          // column distance of adjacent strips of a team
 constexpr int TEAM_SLOTS = TK_WARPS + 2;                 // exchange rows of a CTA: left ghost, its warps, right ghost
 constexpr int TEAM_XROW = 32 * 16;                       // one float4 per lane
-constexpr int TEAM_XPAR = TEAM_SLOTS * TEAM_XROW;        // one parity
-constexpr int TEAM_XBYTES = 2 * TEAM_XPAR;
+constexpr int TEAM_XPAR = 4096;                          // one parity (>= TEAM_SLOTS rows): a power of two, so that
+constexpr int TEAM_XBYTES = 2 * TEAM_XPAR;               // flipping one address bit switches parity (area aligned to 8 KB)
+static_assert(TK_BR % 2 == 0, "a run ends on exchange parity 0");
+static_assert(TEAM_SLOTS * TEAM_XROW <= TEAM_XPAR, "exchange rows of one parity");
+
 constexpr int TEAM_MAX_CLUSTER = 4;
 
 // Columns a team of `warps` strips stores (H = column margin of the OUTER edges).
 __host__ __device__ constexpr int team_cols(int warps, int H) { return TEAM_STRIDE * warps + 8 - 2 * H; }
-__host__ __device__ constexpr int tk_team_smem_bytes() { return tk_smem_ring(LAY_V4) + TK_SMEM_BARS + TEAM_XBYTES; }
+// shared memory of a CTA: TMA ring | mbarriers | slack | exchange area (aligned to its size by the kernel)
+__host__ __device__ constexpr int tk_team_smem_bytes() { return tk_smem_ring(LAY_V4) + TK_SMEM_BARS + 2 * TEAM_XBYTES; }
 
 struct TeamArgs {
   int32_t n_teams;      // teams side by side across the tile (the last one is shifted left to end at the edge)
@@ -62,7 +65,10 @@ struct TeamCtx {
 // one CTA and the hand-over needs a single bar.sync where the others wait.
 template <int CS>
 __device__ __forceinline__ void team_arrive() {
-  if (CS > 1) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+  // membar.cta: this thread's shared-memory store has been performed before the arrive can be
+  // seen (without it a 4-CTA cluster read a stale row once in a 32768^2 sweep); the .release
+  // form of the arrive would add MEMBAR.ALL.GPU, i.e. drain the global stores of every row step
+  if (CS > 1) asm volatile("fence.acq_rel.cta;\n\tbarrier.cluster.arrive.relaxed.aligned;" ::: "memory");
 }
 template <int CS>
 __device__ __forceinline__ void team_wait() {
@@ -106,7 +112,7 @@ __device__ __forceinline__ float4 ld_cluster128(uint32_t addr) {
 template <int K, int ARITH, bool IMM, bool FROZEN, bool FAST, int CS>
 __device__ __forceinline__ void run_task_team(const CUtensorMap* tmap, const TkArgs& a, float* dst_base,
                                               const TeamCtx& tc, int r_lo, int r_hi, uint32_t ring, uint32_t bars,
-                                              int lane, uint32_t& track) {
+                                              int lane, uint32_t& track, int box0 = 0) {
   static_assert(K >= 2, "a team needs two levels to split");
   constexpr bool TRACK = ARITH != H2D_ARITH_FP32;
   constexpr int M = K / 2;                 // levels before the hand-over
@@ -140,8 +146,11 @@ __device__ __forceinline__ void run_task_team(const CUtensorMap* tmap, const TkA
     }
   }
 
+  // box0: boxes this warp's ring has already carried (a task that is run a second time continues
+  // the stage / phase sequence of its mbarriers; the number of row steps of a run is a multiple
+  // of TK_BR = 6, so the exchange parity starts over at 0 as well)
   auto issue = [&](int b) {
-    const int s = b % TK_STAGES;
+    const int s = (box0 + b) % TK_STAGES;
     const uint32_t bar = bars + s * 8;
     mbar_expect_tx(bar, STAGE_BYTES);
     tma_load_2d(ring + s * STAGE_BYTES, tmap, tc0, tc1 + b * TK_BR, bar);
@@ -159,16 +168,22 @@ __device__ __forceinline__ void run_task_team(const CUtensorMap* tmap, const TkA
   int ro = -LAG;
   float* q = dst_base + (int64_t)(g.halo_r + r_lo - LAG) * g.pitch + g.halo_c + j0;
 
-  // One row step; PH = its phase in the 3-slot rotation, PAR = its parity in the exchange area.
-  auto row_step = [&](auto Ptag, auto Qtag) {
+  // Row step i writes parity i & 1 of the exchange area and reads the other one.  The parity is
+  // a run-time address bit, not a template argument: unrolling over 3 rotation phases x 2
+  // parities doubles the loop body, and the strict body then (2 450 instructions, 39 KB) no
+  // longer fits the instruction cache (ncu: no_instruction 0.04 -> 0.88 warps per issue).
+  uint32_t xw = tc.xwr, xr = tc.xrd ^ (uint32_t)TEAM_XPAR;
+
+  // One row step; PH = its phase in the 3-slot rotation.
+  auto row_step = [&](auto Ptag) {
     constexpr int PH = decltype(Ptag)::value;
-    constexpr int PAR = decltype(Qtag)::value;
     constexpr int iu = PH, ic = (PH + 1) % 3, id = (PH + 2) % 3;
     float4 fin;
     if (TRACK) trk = umax4(trk, st[0][id]);
     // everybody's previous row is in the other parity
     team_wait<CS>();
-    const float4 nx = (CS > 1 && tc.remote) ? ld_cluster128(tc.xrd + (PAR ^ 1) * TEAM_XPAR) : lds128(tc.xrd + (PAR ^ 1) * TEAM_XPAR);
+    const float4 nx = (CS > 1 && tc.remote) ? ld_cluster128(xr) : lds128(xr);
+    xr ^= (uint32_t)TEAM_XPAR;
 #pragma unroll
     for (int t = 0; t < K; ++t) {
       const float4 up = st[t][iu];
@@ -193,7 +208,8 @@ __device__ __forceinline__ void run_task_team(const CUtensorMap* tmap, const TkA
       if (t == M) team_arrive<CS>();
       if (t == M - 1) {
         // hand-over
-        sts128(tc.xwr + PAR * TEAM_XPAR, o);
+        sts128(xw, o);
+        xw ^= (uint32_t)TEAM_XPAR;
         st[M][id] = nx;
       } else if (t + 1 < K) {
         st[t + 1][id] = o;
@@ -214,28 +230,20 @@ __device__ __forceinline__ void run_task_team(const CUtensorMap* tmap, const TkA
     q += g.pitch;
     ++ro;
   };
-  using I0 = std::integral_constant<int, 0>;
-  using I1 = std::integral_constant<int, 1>;
-  using I2 = std::integral_constant<int, 2>;
-
 #pragma unroll 1
   for (int b = 0; b < n_blk; ++b) {
-    const int s = b % TK_STAGES;
-    mbar_wait(bars + s * 8, (uint32_t)((b / TK_STAGES) & 1));
+    const int s = (box0 + b) % TK_STAGES;
+    mbar_wait(bars + s * 8, (uint32_t)(((box0 + b) / TK_STAGES) & 1));
     const uint32_t sbase = ring + s * STAGE_BYTES + lane * 16;
-    // six row steps per box: two turns of the 3-slot rotation, three of the parity
-    st[0][2] = lds128(sbase + 0 * (W * 4));
-    row_step(I0{}, I0{});
-    st[0][0] = lds128(sbase + 1 * (W * 4));
-    row_step(I1{}, I1{});
-    st[0][1] = lds128(sbase + 2 * (W * 4));
-    row_step(I2{}, I0{});
-    st[0][2] = lds128(sbase + 3 * (W * 4));
-    row_step(I0{}, I1{});
-    st[0][0] = lds128(sbase + 4 * (W * 4));
-    row_step(I1{}, I0{});
-    st[0][1] = lds128(sbase + 5 * (W * 4));
-    row_step(I2{}, I1{});
+#pragma unroll 1
+    for (int rr = 0; rr < TK_BR; rr += 3) {
+      st[0][2] = lds128(sbase + rr * (W * 4));
+      row_step(std::integral_constant<int, 0>{});
+      st[0][0] = lds128(sbase + (rr + 1) * (W * 4));
+      row_step(std::integral_constant<int, 1>{});
+      st[0][1] = lds128(sbase + (rr + 2) * (W * 4));
+      row_step(std::integral_constant<int, 2>{});
+    }
     __syncwarp();
     if (lane == 0 && b + TK_STAGES < n_blk) issue(b + TK_STAGES);
   }

@@ -64,7 +64,7 @@ class PlanDesc(C.Structure):
         ("scratch", C.c_void_p),
         ("spin_timeout_ns", C.c_int64),
         ("layout", C.c_int32),
-        ("reserved", C.c_int32),
+        ("team", C.c_int32),
         ("colbuf_in", (C.c_void_p * 2) * 2),
     ]
 

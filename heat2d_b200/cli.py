@@ -50,6 +50,9 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--chunk-rows", type=int)
     ap.add_argument("--layout", choices=["auto", "v4", "ab2", "ab4"],
                     help="lane layout of the fp32 kernels (same bits; v4 is the measured best on B200)")
+    ap.add_argument("--team", choices=["on", "off"],
+                    help="on: k >= 5 sweeps of single-GPU runs as cluster launches that share edge columns between "
+                         "strips instead of recomputing them (same bits; pays off in strict arithmetic at >= 32768^2)")
     ap.add_argument("--dataflow", action="store_true",
                     help="single tile, no convergence: all sweeps in one dataflow launch")
     ap.add_argument("--threads", type=int, help="NUMTHREADS (cpu backend)")
@@ -69,7 +72,7 @@ def config_from_args(a) -> HeatConfig:
     over = {}
     for name in ("nx", "ny", "steps", "px", "py", "interval", "eps", "norm", "cx", "cy", "boundary", "arith",
                  "init", "dump", "out_dir", "k", "backend", "chunk_rows", "threads", "restart", "start_step",
-                 "conv_mode", "layout"):
+                 "conv_mode", "layout", "team"):
         v = getattr(a, name, None)
         if v is not None:
             over[name] = v

@@ -60,6 +60,9 @@ class HeatConfig:
                                  # (single tile, no convergence test; h2d_plan_run_dataflow)
     layout: str = "auto"         # lane layout of the fp32 kernels: auto | v4 | ab2 | ab4 (csrc/tk_task.cuh);
                                  # same bits, different speed; strict arithmetic always runs v4
+    team: str = "off"            # on: sweeps of k >= 5 without neighbours / norm run as cluster launches whose
+                                 # strips share their edge columns through shared memory (csrc/tk_team.cuh);
+                                 # same bits; faster only in strict arithmetic on very large tiles
 
     def validate(self, world_size: Optional[int] = None) -> "HeatConfig":
         if self.nx < 1 or self.ny < 1:
@@ -89,6 +92,8 @@ class HeatConfig:
                 raise ConfigError(f"dump must be a comma list of {DUMPS}")
         if self.conv_mode not in CONV_MODES:
             raise ConfigError(f"conv_mode must be one of {CONV_MODES}")
+        if self.team not in ("on", "off"):
+            raise ConfigError("team must be 'on' or 'off'")
         if self.layout not in LAYOUTS:
             raise ConfigError(f"layout must be one of {sorted(LAYOUTS)}")
         if not 1 <= self.k <= KMAX:

@@ -138,8 +138,9 @@ class TileEngine:
 
     def __init__(self, field: TileField, phys: N.Phys, kmax: int, chunk_rows: int, world: int,
                  rank: int, flags_in: torch.Tensor, vals: torch.Tensor, nflags: torch.Tensor,
-                 spin_timeout_s: float = 10.0, layout: int = 0):
+                 spin_timeout_s: float = 10.0, layout: int = 0, team: int = 0):
         self.field = field
+        self.team = team
         self.phys = phys
         self.kmax = kmax
         self.chunk_rows = chunk_rows
@@ -160,7 +161,7 @@ class TileEngine:
         f = self.field
         self.plan = K.Plan(f.tile, self.phys, f.buf[0].data_ptr(), f.buf[1].data_ptr(), self.kmax,
                            self.chunk_rows, peers=peers, flags_in_ptr=self.flags_in.data_ptr(),
-                           spin_timeout_s=self.spin_timeout_s, device=f.device, layout=self.layout,
+                           spin_timeout_s=self.spin_timeout_s, device=f.device, layout=self.layout, team=self.team,
                            colbuf_in=[[f.colbuf[side][par].data_ptr() if peers.get(d) is not None else 0
                                        for par in (0, 1)] for side, d in ((0, "W"), (1, "E"))])
         self.vals_ptrs = torch.tensor(all_vals_ptrs, dtype=torch.int64, device=f.device)
@@ -256,7 +257,7 @@ class Heat2DSolver:
             vals = torch.zeros(2 * w, dtype=torch.float32, device=dev)
             nflags = torch.zeros(2 * w, dtype=torch.int32, device=dev)
             self.engines.append(TileEngine(f, self.phys, max(cfg.k, 1), cfg.chunk_rows, w, r, flags_in,
-                                           vals, nflags, cfg.spin_timeout_s, _layout_code(cfg)))
+                                           vals, nflags, cfg.spin_timeout_s, _layout_code(cfg), int(cfg.team == "on")))
         all_vals = [e.vals.data_ptr() for e in self.engines]
         all_nfl = [e.nflags.data_ptr() for e in self.engines]
         for r, e in enumerate(self.engines):

@@ -167,7 +167,7 @@ class Plan:
     def __init__(self, tile: N.Tile, phys: N.Phys, buf0_ptr: int, buf1_ptr: int, kmax: int,
                  chunk_rows: int = 0, peers: Optional[dict] = None, flags_in_ptr: int = 0,
                  scratch_ptr: int = 0, spin_timeout_s: float = 10.0, device=None, layout: int = 0,
-                 colbuf_in=None):
+                 colbuf_in=None, team: int = 0):
         self._lib = N.cuda()
         self.tile, self.phys, self.kmax = tile, phys, kmax
         self.device = device
@@ -193,6 +193,7 @@ class Plan:
         d.scratch = scratch_ptr or None
         d.spin_timeout_ns = int(spin_timeout_s * 1e9)
         d.layout = int(layout)
+        d.team = int(team)     # eligible sweeps as cluster launches (h2d_plan_desc_t::team)
         if colbuf_in is not None:      # [[west parity 0, west parity 1], [east parity 0, east parity 1]]
             for side in (0, 1):
                 for par in (0, 1):

@@ -147,7 +147,7 @@ class DistributedHeat2DSolver(Heat2DSolver):
         vals = tensor_from_ptr(a.ptr + a.off_vals, (2 * w,), torch.float32, dev, owner=a)
         nflags = tensor_from_ptr(a.ptr + a.off_nflags, (2 * w,), torch.int32, dev, owner=a)
         eng = TileEngine(f, self.phys, cfg.k, cfg.chunk_rows, w, r, flags_in, vals, nflags,
-                         cfg.spin_timeout_s, _layout_code(cfg))
+                         cfg.spin_timeout_s, _layout_code(cfg), int(cfg.team == "on"))
         self.engines = [eng]
 
         # exchange handles + geometry (start-up only)

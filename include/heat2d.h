@@ -198,7 +198,12 @@ typedef struct h2d_plan_desc {
    * 128-column strips), 2 = ab2 / 3 = ab4 (two half-strips packed in f32x2, 128- /
    * 256-column strips).  Strict arithmetic always uses v4.  Results are bit-identical. */
   int32_t layout;
-  int32_t reserved;
+  /* != 0: k-step sweeps (k >= 5) of a plan without neighbours, launched without a norm, go out as
+   * cluster launches whose strips exchange their edge columns through shared memory instead of
+   * recomputing them (h2d_plan_launch_team with one CTA per team; tiles narrower than 472
+   * columns and all other launches are unaffected).  Same bits.  Measured on B200 in strict-fma:
+   * 3-7 % faster at 32768^2, 2 % at 16384^2 with short tasks, slower below; fp32: 3-4 % slower. */
+  int32_t team;
   /* Packed column-ghost buffers of THIS rank, [side][parity] (side 0 = ghosts west of the
    * tile, 1 = east), each rows x 8 floats, in memory the W / E neighbour can reach (it gets
    * the pointers as its h2d_peer_t::colbuf).  The neighbour writes its k edge columns of tile
@@ -271,11 +276,12 @@ int h2d_plan_run_dataflow(h2d_plan_t* plan, int src_parity, int k, int n_epochs,
  * the strips of a team advance in row lock-step and hand each other their edge columns
  * half-way through the k levels — through shared memory inside a CTA, through distributed
  * shared memory between the CTAs — so that adjacent strips overlap by 8 columns instead of
- * 16 (csrc/tk_team.cuh).  Single-tile plans, v4 lane layout, fp32 and strict-fma arithmetic,
+ * 16 (csrc/tk_team.cuh).  Single-tile plans, v4 lane layout, fp32 / strict-fma (strict: cluster = 1),
  * no norm.  chunk_rows = 0 picks the task height.  Same result, bit for bit, as
- * h2d_plan_launch; in strict-fma, data outside the domain of the fast evaluation is COUNTED
- * (h2d_plan_team_fallback_ptr) instead of re-evaluated: repeat the sweep with h2d_plan_launch
- * if the counter moved.  The reference has one thread per point and no reuse
+ * h2d_plan_launch.  Strict arithmetic: strips whose data left the domain of the fast evaluation
+ * are counted (h2d_plan_team_fallback_ptr); a one-CTA team (cluster = 1) then runs its task
+ * again with the plain evaluation, larger clusters leave that to the caller (repeat the sweep
+ * with h2d_plan_launch if the counter moved).  The reference has one thread per point and no reuse
  * (grad1612_cuda_heat.cu:55-62).                                                     */
 int h2d_plan_launch_team(h2d_plan_t* plan, int src_parity, int k, int cluster, int chunk_rows, void* stream);
 uint32_t* h2d_plan_team_fallback_ptr(h2d_plan_t* plan);

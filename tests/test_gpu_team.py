@@ -66,6 +66,41 @@ def test_team_launch_counts_data_outside_the_fast_strict_domain():
     assert fb > 0
 
 
+@pytest.mark.parametrize("arith", ["strict", "strict-fma"])
+def test_one_cta_teams_redo_tasks_outside_the_fast_strict_domain(arith):
+    # negative, infinite and NaN cells: the teams that see them run again with the plain evaluation
+    nx, ny = 150, 1500
+    u0 = (np.random.default_rng(5).random((nx, ny), dtype=np.float32) * 100).astype(np.float32)
+    u0[20:30, 500:520] *= np.float32(-1.0)
+    u0[100, 1200] = np.float32("inf")
+    got, fb = run_team(u0, 8, 2, 1, "fixed", arith, chunk_rows=48)
+    want = oracle(u0, 16, "fixed", arith)
+    assert fb > 0
+    gn, wn = np.isnan(got), np.isnan(want)
+    assert wn.any() and np.array_equal(gn, wn)
+    assert np.array_equal(got.view(np.uint32)[~gn], want.view(np.uint32)[~wn])
+
+
+@pytest.mark.parametrize("arith", ["fp32", "strict-fma"])
+@pytest.mark.parametrize("conv", [False, True])
+def test_solver_with_team_launches(arith, conv):
+    # HeatConfig.team = "on": the k >= 5 sweeps without a norm are cluster launches, the checked
+    # sweeps and the k < 5 remainder are not; same schedule, same bits, same stopping step
+    nx, ny = 300, 1000
+    u0 = K.cpu_initial_grid(nx, ny, "exact")
+    cfg = HeatConfig(nx=nx, ny=ny, steps=131, k=8, arith=arith, team="on", conv=conv, interval=20, eps=1e-3,
+                     boundary="ghost-ring")
+    s = Heat2DSolver(cfg, DEV).initialize()
+    res = s.run()
+    ref = u0.copy()
+    done, _ = K.cpu_run(ref, 131, N.make_phys(0.1, 0.1, "ghost-ring", arith), "l2sq" if conv else "none", 20, 1e-3)
+    assert res.steps_done == done
+    assert np.array_equal(s.gather().numpy(), ref)
+    # and the team kernels really ran
+    assert s.engines[0].plan._desc.team == 1
+    s.close()
+
+
 def test_team_launch_rejects_what_it_cannot_do():
     s = Heat2DSolver(HeatConfig(nx=64, ny=300, steps=8, k=8, layout="v4"), DEV).initialize()
     with pytest.raises(RuntimeError, match="narrower than one team"):

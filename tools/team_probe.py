@@ -42,6 +42,8 @@ def main():
     ap.add_argument("--clusters", default="1,2,4")
     ap.add_argument("--ks", default="8")
     ap.add_argument("--chunks", default="0")
+    ap.add_argument("--checks", type=int, default=4)
+    ap.add_argument("--tag", default="")
     a = ap.parse_args()
     n = a.n
     out = []
@@ -67,11 +69,13 @@ def main():
             print(rec, flush=True)
             for cl in map(int, a.clusters.split(",")):
                 for ch in map(int, a.chunks.split(",")):
-                    f.buf[0].copy_(init)
-                    f.buf[1].zero_()
-                    e.plan.launch_team(0, k, cl, ch)
-                    torch.cuda.synchronize()
-                    same = bool(torch.equal(f.owned(1), want))
+                    same = True
+                    for _ in range(a.checks):
+                        f.buf[0].copy_(init)
+                        f.buf[1].zero_()
+                        e.plan.launch_team(0, k, cl, ch)
+                        torch.cuda.synchronize()
+                        same = same and bool(torch.equal(f.owned(1), want))
 
                     def team(par, cl=cl, ch=ch):
                         return e.plan.launch_team(par, k, cl, ch)
@@ -86,7 +90,7 @@ def main():
             del s, e, f, init, want
             torch.cuda.empty_cache()
     os.makedirs("gpurun_out", exist_ok=True)
-    with open(f"gpurun_out/team_probe_{n}.json", "w") as fo:
+    with open(f"gpurun_out/team_probe_{n}{a.tag}.json", "w") as fo:
         json.dump(out, fo, indent=1)
 
 
