@@ -1,3 +1,5 @@
+# gpurun payload: ncu --set full captures of the flagship kernels (plain, strict, forwarding, norm finish).
+# usage: gpurun -- 'bash tools/gpu_ncu_final.sh'
 set -x
 timeout 900 python -m pytest tests -m gpu -q --timeout=120 -x > gpurun_out/gputest17.log 2>&1; echo "rc=$?" >> gpurun_out/gputest17.log; tail -4 gpurun_out/gputest17.log
 timeout 300 python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/bench_ref_final.log 2>&1; tail -1 gpurun_out/bench_ref_final.log | cut -c1-300

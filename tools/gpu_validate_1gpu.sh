@@ -1,3 +1,4 @@
+# gpurun payload: the whole -m gpu suite, smoke(), both bench arms and an ncu capture of the team kernels on ONE GPU.
 set -x
 timeout 1200 python -m pytest tests -m gpu -q --timeout=120 -x > gpurun_out/gputest_final.log 2>&1; echo "rc=$?" >> gpurun_out/gputest_final.log; tail -6 gpurun_out/gputest_final.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
