@@ -59,7 +59,9 @@ def parse_args(argv=None):
     ap.add_argument("--warmup", type=int, default=24)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl-halo"])
     ap.add_argument("--grid", type=int, default=32768, help="NX = NY (32768: config 3, 16384: config 2)")
-    ap.add_argument("--k", type=int, default=8, help="time steps per launch / halo exchange")
+    ap.add_argument("--k", type=int, default=0, help="time steps per launch / halo exchange; 0 = the depth "
+                    "heat2d_b200.config.best_k picks for the arithmetic and the tile size (fp32: 8; strict: 4 on "
+                    "tiles of 2^28 cells or more, else 8)")
     ap.add_argument("--chunk-rows", type=int, default=0)
     ap.add_argument("--arith", default="strict-fma", choices=["strict-fma", "strict", "fp32"],
                     help="arithmetic of the headline value (strict-fma = the reference CUDA build's bits)")
@@ -374,7 +376,10 @@ def main(argv=None):
         px, py = d.px, d.py
     nx, ny = (n * px, n * py) if a.weak else (n, n)
     backend = "nccl-halo" if a.impl == "nccl-halo" else "fused"
-    k = a.k   # nccl-halo: --k 8 = same kernel + grouped NCCL exchange of 8-wide bands; --k 1 = one cell per step
+    from heat2d_b200.config import best_k
+    tile_pts = (nx * ny) // (px * py)
+    # nccl-halo: --k 8 = same kernel + grouped NCCL exchange of 8-wide bands; --k 1 = one cell per step
+    k = a.k or (8 if backend == "nccl-halo" else best_k(a.arith, tile_pts))
     cfg = HeatConfig(nx=nx, ny=ny, steps=a.steps, px=px, py=py, k=k, halo=max(k, 8), arith=a.arith,
                      boundary="fixed", init="exact", backend=backend, chunk_rows=a.chunk_rows,
                      conv=a.conv, interval=20, eps=0.0 if a.conv else 0.1, conv_mode="exact")
@@ -410,28 +415,29 @@ def main(argv=None):
 
     extra = None
     if other is not None:
-        cfg2 = cfg.replace(arith=other)
+        cfg2 = cfg.replace(arith=other, k=a.k or best_k(other, tile_pts))
         s2 = _make_solver(cfg2, world, device, backend).initialize()
         r2, l2, c2 = _time_run(s2, a.steps, a.warmup, world, device, local)
         g2 = nx * ny * a.steps / r2.elapsed_s / 1e9
-        extra = {"arith": other, "value": g2, "unit": "GLUP/s", "ms_per_step": r2.elapsed_s / a.steps * 1e3,
+        extra = {"arith": other, "k": cfg2.k, "value": g2, "unit": "GLUP/s", "ms_per_step": r2.elapsed_s / a.steps * 1e3,
                  "gpu_launches": l2, "clocks": c2,
-                 "roofline": _roofline(g2, nx, ny, px, py, k, a.chunk_rows) if other == "fp32" else None}
+                 "roofline": _roofline(g2, nx, ny, px, py, cfg2.k, a.chunk_rows) if other == "fp32" else None}
         getattr(s2, "close", lambda: None)()
         del s2
         torch.cuda.empty_cache()
 
     team = None
-    if world == 1 and backend == "fused" and not a.no_extra and a.arith != "fp32" and k >= 5 and not a.conv:
+    if world == 1 and backend == "fused" and not a.no_extra and a.arith != "fp32" and not a.conv:
         # opt-in launch mode (--team on / HeatConfig.team): the strips of a CTA share their edge
         # columns through shared memory instead of recomputing them; same bits (verified in
         # tests/test_gpu_team.py).  Not the default — it pays off only on tiles this large — so it
         # is reported next to the headline, not as the headline.
-        s3 = _make_solver(cfg.replace(team="on"), world, device, backend).initialize()
+        s3 = _make_solver(cfg.replace(team="on", k=8), world, device, backend).initialize()
         r3, l3, _ = _time_run(s3, a.steps, a.warmup, world, device, local)
-        team = {"arith": a.arith, "value": nx * ny * a.steps / r3.elapsed_s / 1e9, "unit": "GLUP/s",
+        team = {"arith": a.arith, "k": 8, "value": nx * ny * a.steps / r3.elapsed_s / 1e9, "unit": "GLUP/s",
                 "ms_per_step": r3.elapsed_s / a.steps * 1e3, "gpu_launches": l3,
-                "what": "the same run with HeatConfig.team='on' (cluster launches, csrc/tk_team.cuh)"}
+                "what": "the same run at k = 8 with HeatConfig.team='on' (strips of a CTA share their edge "
+                        "columns, csrc/tk_team.cuh) — the other way to cut the recomputed overlap"}
         getattr(s3, "close", lambda: None)()
         del s3
         torch.cuda.empty_cache()

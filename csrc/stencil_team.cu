@@ -143,6 +143,18 @@ int h2d_plan_launch_team(h2d_plan_t* p, int src_parity, int k, int cluster, int 
   return h2d_plan_launch_team_ex(p, src_parity, k, cluster, chunk_rows, nullptr, 0u, stream);
 }
 
+// Opt in to the dynamic shared memory size of the one-CTA team kernels a plan with
+// h2d_plan_desc_t::team may launch — which also loads them, so that the first timed sweep
+// does not pay for it (lazy module loading cost 1.8 ms of a 16 ms run).
+void h2d_plan_team_prepare(const h2d_plan_t* p) {
+  if (!p) return;
+  const bool imm = coef_is_reference(p->geo, p->desc.phys.arith);
+  for (int k = 5; k <= p->desc.kmax && k <= TK_KMAX; ++k) {
+    tk_team_fn_t fn = team_pick(k, p->desc.phys.arith, imm, 1);
+    if (fn) cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, tk_team_smem_bytes());
+  }
+}
+
 int h2d_plan_team_eligible(const h2d_plan_t* p, int k, int cluster) {
   if (!p || p->has_peers || p->lay != LAY_V4 || k < 5 || k > p->desc.kmax || k > TK_KMAX) return 0;
   if (p->desc.phys.arith != H2D_ARITH_FP32 && p->desc.phys.arith != H2D_ARITH_STRICT_FMA &&

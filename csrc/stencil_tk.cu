@@ -436,6 +436,7 @@ h2d_plan_t* h2d_plan_create(const h2d_plan_desc_t* d) {
                            tk_smem_bytes(p->lay, x != 0));
     }
   }
+  if (d->team != 0) h2d_plan_team_prepare(p);   // same for the team kernels it may launch
   return p;
 }
 

@@ -62,6 +62,7 @@ int tk_debug_flags();
 }  // namespace h2d
 
 // stencil_team.cu
+extern "C" void h2d_plan_team_prepare(const h2d_plan_t* plan);
 extern "C" int h2d_plan_team_eligible(const h2d_plan_t* plan, int k, int cluster);
 extern "C" int h2d_plan_launch_team_ex(h2d_plan_t* plan, int src_parity, int k, int cluster, int chunk_rows,
                                        const uint32_t* ctl, uint32_t run_if, void* stream);

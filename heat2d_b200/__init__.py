@@ -8,10 +8,10 @@ Public surface::
 Sub-packages: ``models`` (solvers), ``ops`` (kernel bindings), ``parallel``
 (decomposition, peer memory, multi-GPU solvers), ``utils`` (dumps, timing, clocks).
 """
-from .config import HeatConfig, ConfigError, Launch, make_schedule
+from .config import HeatConfig, ConfigError, Launch, best_k, make_schedule
 
 __version__ = "0.1.0"
-__all__ = ["HeatConfig", "ConfigError", "Launch", "make_schedule", "Heat2DSolver", "CpuSolver", "solve",
+__all__ = ["HeatConfig", "ConfigError", "Launch", "best_k", "make_schedule", "Heat2DSolver", "CpuSolver", "solve",
            "__version__"]
 
 

@@ -45,7 +45,8 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--init", choices=["ref-int32", "ref-uint32", "exact", "zero"])
     ap.add_argument("--dump", help="comma list of none|prtdat|rowmajor|binary")
     ap.add_argument("--out-dir")
-    ap.add_argument("-k", type=int, help="time steps per launch / halo exchange (1..8)")
+    ap.add_argument("-k", type=int, help="time steps per launch / halo exchange (1..8); default: 8, or — without "
+                                         "a preset — what is fastest for the arithmetic and tile size (config.best_k)")
     ap.add_argument("--backend", choices=BACKENDS)
     ap.add_argument("--chunk-rows", type=int)
     ap.add_argument("--layout", choices=["auto", "v4", "ab2", "ab4"],
@@ -89,6 +90,9 @@ def config_from_args(a) -> HeatConfig:
     if a.ref_conv_bug:
         over["ref_conv_bug"] = True
     cfg = cfg.replace(**over)
+    if a.k is None and not a.preset:
+        from .config import best_k
+        cfg = cfg.replace(k=best_k(cfg.arith, (cfg.nx * cfg.ny) // max(cfg.px * cfg.py, 1)))
     if cfg.halo < cfg.k:
         cfg = cfg.replace(halo=cfg.k)
     return cfg

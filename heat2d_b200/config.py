@@ -23,6 +23,21 @@ class ConfigError(ValueError):
     pass
 
 
+def best_k(arith: str, tile_points: int) -> int:
+    """Sweep depth (time steps per launch) with the highest measured throughput on B200 for a
+    tile of `tile_points` cells per GPU.  fp32: 8 — the kernel needs the 8-fold cut in HBM
+    traffic.  Strict arithmetic is bound by instruction dispatch, not by HBM (DRAM 17 % busy at
+    k = 8), and k = 4 recomputes 8 of every 128 columns instead of 16 and fills its pipeline
+    in 8 rows instead of 16: strict-fma 1363 vs 1322 GLUP/s at 32768^2 (20 steps: 1361 vs 1294,
+    since 20 = 5 x 4 but 7 + 7 + 6), 1320 vs 1264 at 16384^2, 5215 vs 5010 on 2 x 2 GPUs — and
+    nothing on 8192 x 16384 tiles (1220 vs 1219), where twice the launches and halo exchanges
+    would only cost (profiles/r2/probe_strict-fma_*_ksweep.json, scaling_sweep_n4_ks.jsonl).
+    k = 3 and k = 2 are slower everywhere."""
+    if arith == "fp32":
+        return 8
+    return 4 if tile_points >= (1 << 28) else 8
+
+
 @dataclass
 class HeatConfig:
     """Everything a run needs.  Defaults are the reference's defaults."""

@@ -56,6 +56,9 @@ def _cases(px, py):
         {"name": "fused-k8-ab4", "random": True, "cfg": dict(base, steps=41, backend="fused", layout="ab4")},
         {"name": "fused-strict-fma-mixed-sign", "random": True, "negative": True,
          "cfg": dict(base, steps=24, backend="fused", arith="strict-fma")},
+        # k = 4: what best_k picks for strict arithmetic on large tiles (bench.py's headline)
+        {"name": "fused-strict-fma-k4", "random": True, "cfg": dict(base, steps=42, backend="fused", k=4,
+                                                                     arith="strict-fma")},
     ]
 
 
@@ -107,6 +110,9 @@ def test_pipelined_solve_on_column_strips(delay):
         # ghost columns and must take part in the flag protocol as well
         {"name": "pipelined-k8-narrow-last-strip", "random": True, "pipelined": True,
          "cfg": dict(nx=2000, ny=228 * n, px=1, py=n, k=8, steps=50, backend="fused", chunk_rows=48, layout="v4")},
+        # the sweep depth of bench.py's end-to-end run on large tiles (strict arithmetic, k = 4)
+        {"name": "pipelined-k4-strict-fma", "random": True, "pipelined": True,
+         "cfg": dict(nx=2500, ny=256 * n, px=1, py=n, k=4, steps=20, backend="fused", arith="strict-fma")},
     ]
     out = _run(n, {"cases": cases}, env_extra={"H2D_DEBUG_DELAY": "1"} if delay else None)
     assert out["ok"], out

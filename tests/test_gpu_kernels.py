@@ -317,6 +317,8 @@ def test_halo_wait_statistics_are_exposed():
 
 
 @pytest.mark.parametrize("shape,steps,k,block,skew", [((700, 900), 83, 8, 96, 32), ((1030, 2050), 41, 5, 0, 0),
+                                                      ((900, 1300), 42, 4, 0, 0), ((515, 777), 20, 4, 64, 0),
+                                                      ((400, 600), 31, 3, 0, 0),
                                                       ((257, 391), 24, 8, 64, 9), ((300, 500), 0, 8, 0, 0)])
 def test_pipelined_upload_solve_download(shape, steps, k, block, skew):
     # blocks run all their launches before the next block starts (skewed windows):
@@ -348,7 +350,8 @@ def test_solve_api_uses_the_pipelined_path_for_pinned_input():
 
 
 @pytest.mark.parametrize("py,shape,steps,k,block", [(2, (1500, 512), 83, 8, 0), (3, (900, 768), 41, 5, 128),
-                                                    (4, (2200, 1024), 24, 8, 256),
+                                                    (4, (2200, 1024), 24, 8, 256), (2, (1100, 640), 42, 4, 0),
+                                                    (3, (800, 900), 20, 4, 96),
                                                     # 228 columns per tile: the last task strip owns 4 < k
                                                     # columns, the strip before it reads the E ghosts too
                                                     (2, (1200, 456), 50, 8, 0)])

@@ -49,3 +49,10 @@ def test_config_validation_messages():
         HeatConfig(arith="fp16").validate()
     c = HeatConfig(cx_float=True)
     assert c.cx_eff != 0.1 and abs(c.cx_eff - 0.1) < 1e-8
+
+
+def test_best_k_follows_the_measurements():
+    from heat2d_b200 import best_k
+    assert best_k("fp32", 1 << 30) == 8 and best_k("fp32", 1 << 20) == 8
+    assert best_k("strict-fma", 32768 * 32768) == 4 and best_k("strict", 16384 * 16384) == 4
+    assert best_k("strict-fma", 8192 * 16384) == 8      # an eighth of 32768^2: one tile of an 8-GPU run

@@ -29,6 +29,7 @@ def main():
     ap.add_argument("--steps", type=int, default=1000)
     ap.add_argument("--warmup", type=int, default=24)
     ap.add_argument("--k", type=int, default=8)
+    ap.add_argument("--ks", default="", help="comma list of sweep depths (overrides --k)")
     ap.add_argument("--layouts", default="")
     ap.add_argument("--min-waves", default="4")
     ap.add_argument("--ariths", default="fp32")
@@ -44,7 +45,9 @@ def main():
     if rank == 0:
         os.makedirs("gpurun_out", exist_ok=True)
     n = a.grid
-    for backend in a.backends.split(","):
+    ks = [int(v) for v in a.ks.split(",") if v] or [a.k]
+    for backend in [(b, kk) for b in a.backends.split(",") for kk in ks]:
+        backend, a.k = backend
         for arith in a.ariths.split(","):
             for px, py in layouts:
                 if px * py != world:
