@@ -326,18 +326,28 @@ def _e2e(a, cfg, solver, world, rank, device, steps, verified_pipe):
         dev_out = torch.empty(tuple(host_out.shape), dtype=torch.float32, device=device)
         s_up, s_dn = torch.cuda.Stream(device), torch.cuda.Stream(device)
 
-        def links():
+        def links(up=True, dn=True):
             s_up.wait_stream(torch.cuda.current_stream(device))
             s_dn.wait_stream(torch.cuda.current_stream(device))
-            with torch.cuda.stream(s_up):
-                dev_in.copy_(host_in, non_blocking=True)
-            with torch.cuda.stream(s_dn):
-                host_out.copy_(dev_out, non_blocking=True)
+            if up:
+                with torch.cuda.stream(s_up):
+                    dev_in.copy_(host_in, non_blocking=True)
+            if dn:
+                with torch.cuda.stream(s_dn):
+                    host_out.copy_(dev_out, non_blocking=True)
             torch.cuda.current_stream(device).wait_stream(s_up)
             torch.cuda.current_stream(device).wait_stream(s_dn)
-        link_s = min(timed(links)[0] for _ in range(2))
-        here = (host_in.numel() + host_out.numel()) * 4 * world / link_s / 1e9
-        out["pcie_both_directions_gbs_this_run"] = here
+        both_s = min(timed(links)[0] for _ in range(2))
+        up_s = timed(lambda: links(True, False))[0]
+        dn_s = timed(lambda: links(False, True))[0]
+        # the floor of an upload + download of these bytes on this box: both directions at once,
+        # or one after the other where the host side handles that better (seen with 8 ranks)
+        link_s = min(both_s, up_s + dn_s)
+        nbytes = (host_in.numel() + host_out.numel()) * 4 * world
+        out["pcie_both_directions_gbs_this_run"] = nbytes / both_s / 1e9
+        out["pcie_h2d_gbs_this_run"] = host_in.numel() * 4 * world / up_s / 1e9
+        out["pcie_d2h_gbs_this_run"] = host_out.numel() * 4 * world / dn_s / 1e9
+        out["pcie_floor_seconds_this_run"] = link_s
         # the headline fraction is against THIS box's links (119-176 GB/s seen on 4-GPU boxes of the
         # pool); e2e_roofline_vs_profile keeps the one against profiles/pcie_peaks.json
         out["e2e_roofline"] = out["e2e_roofline_this_box"] = link_s / e2e_s
