@@ -189,6 +189,8 @@ int h2d_plan_launch_team_ex(h2d_plan_t* p, int src_parity, int k, int cluster, i
   // chunk height: whole waves of clusters, the pipeline fill (2k + 9 row steps) weighed against
   // the last, partly empty wave — the rule of choose_chunk_rows with teams for strips
   int R = chunk_rows;
+  int& cached = p->team_rows[k - 5][cluster == 1 ? 0 : (cluster == 2 ? 1 : 2)];
+  if (R <= 0) R = cached;
   if (R <= 0) {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
@@ -206,6 +208,7 @@ int h2d_plan_launch_team_ex(h2d_plan_t* p, int src_parity, int k, int cluster, i
       const double cost = (waves + 0.5) * (double)(r + 2 * k + 9);
       if (cost < best * (1.0 - 1e-9)) { best = cost; R = r; }
     }
+    cached = R;   // the search walks up to `rows` candidates: once per plan, k and cluster size
   }
   ta.chunk_rows = R;
   ta.n_chunks = (t.rows + R - 1) / R;

@@ -27,6 +27,8 @@ struct h2d_plan {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   int device = 0;
   bool has_peers = false;
+  // task height of team launches, [k - 5][cluster 1 / 2 / 4]; 0 = not chosen yet (stencil_team.cu)
+  int team_rows[4][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
   // lazily created by h2d_plan_run_dataflow: [0] ticket, [64...] done[] per task
   uint32_t* flow = nullptr;
   size_t flow_tasks = 0;
