@@ -61,7 +61,7 @@ def parse_args(argv=None):
     ap.add_argument("--grid", type=int, default=32768, help="NX = NY (32768: config 3, 16384: config 2)")
     ap.add_argument("--k", type=int, default=0, help="time steps per launch / halo exchange; 0 = the depth "
                     "heat2d_b200.config.best_k picks for the arithmetic and the tile size (fp32: 8; strict: 4 on "
-                    "tiles of 2^28 cells or more, else 8)")
+                    "tiles of 2^27 cells or more, else 8)")
     ap.add_argument("--chunk-rows", type=int, default=0)
     ap.add_argument("--arith", default="strict-fma", choices=["strict-fma", "strict", "fp32"],
                     help="arithmetic of the headline value (strict-fma = the reference CUDA build's bits)")

@@ -38,8 +38,12 @@ static tk_fn_t tk_pick_x(int k, int arith, int lay, bool imm) {
         case LAY_AB4: return tk_get<H2D_ARITH_FP32, LAY_AB4, XTR>(k, imm);
         default: return nullptr;
       }
-    case H2D_ARITH_STRICT: return lay == LAY_V4 ? tk_get<H2D_ARITH_STRICT, LAY_V4, XTR>(k, false) : nullptr;
-    case H2D_ARITH_STRICT_FMA: return lay == LAY_V4 ? tk_get<H2D_ARITH_STRICT_FMA, LAY_V4, XTR>(k, false) : nullptr;
+    case H2D_ARITH_STRICT:
+      return lay == LAY_V4 ? tk_get<H2D_ARITH_STRICT, LAY_V4, XTR>(k, false)
+           : lay == LAY_V8 ? tk_get<H2D_ARITH_STRICT, LAY_V8, XTR>(k, false) : nullptr;
+    case H2D_ARITH_STRICT_FMA:
+      return lay == LAY_V4 ? tk_get<H2D_ARITH_STRICT_FMA, LAY_V4, XTR>(k, false)
+           : lay == LAY_V8 ? tk_get<H2D_ARITH_STRICT_FMA, LAY_V8, XTR>(k, false) : nullptr;
     default: return nullptr;
   }
 }
@@ -113,9 +117,29 @@ static int default_fp32_layout() {
   }
   return lay;
 }
-static int pick_layout(int arith, int requested) {
-  if (arith != H2D_ARITH_FP32) return LAY_V4;
-  if (requested >= 1 && requested <= LAY_COUNT) return requested - 1;
+// Strict modes: their arithmetic is scalar, so V4 — or, for plans whose sweeps are at most 4
+// levels deep, V8 (8 columns per lane).  Default for those: H2D_STRICT_LAYOUT=v4|v8, else the
+// measured best (build.py passes V8: strict-fma, k = 4, 32768^2 1438 vs 1366 GLUP/s, 8192 x 16384
+// 1280 vs 1219, 16384^2 1322 vs 1320).
+#ifndef H2D_DEFAULT_STRICT_SHALLOW_LAYOUT
+#define H2D_DEFAULT_STRICT_SHALLOW_LAYOUT LAY_V4
+#endif
+static int default_strict_shallow_layout() {
+  static int lay = -1;
+  if (lay < 0) {
+    lay = H2D_DEFAULT_STRICT_SHALLOW_LAYOUT;
+    const char* e = getenv("H2D_STRICT_LAYOUT");
+    if (e && !strcmp(e, "v4")) lay = LAY_V4;
+    if (e && !strcmp(e, "v8")) lay = LAY_V8;
+  }
+  return lay;
+}
+static int pick_layout(int arith, int requested, int kmax) {
+  if (arith != H2D_ARITH_FP32) {
+    if (kmax > TK_V8_KMAX || requested == LAY_V4 + 1) return LAY_V4;
+    return requested == LAY_V8 + 1 ? LAY_V8 : default_strict_shallow_layout();
+  }
+  if (requested >= 1 && requested <= LAY_AB4 + 1) return requested - 1;
   return default_fp32_layout();
 }
 
@@ -292,14 +316,16 @@ extern "C" {
 int32_t h2d_plan_chunk_rows_ex(const h2d_tile_t* tile, int32_t kmax, int32_t with_peers, int32_t arith,
                                int32_t layout) {
   if (!tile || kmax < 1 || kmax > TK_KMAX || tile->rows < 1 || tile->cols < 1) return 0;
-  return choose_chunk_rows(tile->rows, tile->cols, kmax, pick_layout(arith, layout), with_peers ? peer_min_waves() : 1);
+  return choose_chunk_rows(tile->rows, tile->cols, kmax, pick_layout(arith, layout, kmax), with_peers ? peer_min_waves() : 1);
 }
 
 int32_t h2d_plan_chunk_rows(const h2d_tile_t* tile, int32_t kmax, int32_t with_peers) {
   return h2d_plan_chunk_rows_ex(tile, kmax, with_peers, H2D_ARITH_FP32, 0);
 }
 
-int32_t h2d_plan_strip_width(int32_t arith, int32_t layout) { return tk_strip_width(pick_layout(arith, layout)); }
+int32_t h2d_plan_strip_width(int32_t arith, int32_t layout) {
+  return tk_strip_width(pick_layout(arith, layout, layout == LAY_V8 + 1 ? TK_V8_KMAX : TK_KMAX));
+}
 
 size_t h2d_plan_scratch_bytes(const h2d_tile_t* tile, int32_t kmax, int32_t chunk_rows) {
   if (!tile || kmax < 1 || kmax > TK_KMAX || tile->rows < 1 || tile->cols < 1) return 0;
@@ -386,7 +412,7 @@ h2d_plan_t* h2d_plan_create(const h2d_plan_desc_t* d) {
   p->desc = *d;
   p->geo = make_geo(t, d->phys);
   p->has_peers = has_peers;
-  p->lay = pick_layout(d->phys.arith, d->layout);
+  p->lay = pick_layout(d->phys.arith, d->layout, d->kmax);
   cudaGetDevice(&p->device);
   int max_tasks = 0;
   const int min_waves = has_peers ? peer_min_waves() : 1;

@@ -14,10 +14,14 @@
 
 namespace h2d {
 
+// the 8-column layout exists for sweeps of at most TK_V8_KMAX levels
+constexpr int INST_KMAX = H2D_INST_LAY == LAY_V8 ? TK_V8_KMAX : TK_KMAX;
+
 template <int K, bool IMM>
 static tk_fn_t one() {
-  if (K < H2D_TK_KMIN) return nullptr;
-  return tk_kernel<(K < H2D_TK_KMIN ? H2D_TK_KMIN : K), H2D_INST_ARITH, H2D_INST_LAY, IMM, (H2D_INST_XTR != 0)>;
+  if (K < H2D_TK_KMIN || K > INST_KMAX) return nullptr;
+  constexpr int KK = K < H2D_TK_KMIN ? H2D_TK_KMIN : (K > INST_KMAX ? INST_KMAX : K);
+  return tk_kernel<KK, H2D_INST_ARITH, H2D_INST_LAY, IMM, (H2D_INST_XTR != 0)>;
 }
 
 template <bool IMM>

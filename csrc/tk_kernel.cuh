@@ -17,12 +17,12 @@ namespace h2d {
 // with __maxnreg__ 152 / 144 (32-72 B of spills) 4.31 TLUP/s; 16 warps at 128 registers
 // (244 B of spills) 3.9 TLUP/s.
 // AB4 (24 state registers per level): 2 CTAs = 8 warps per SM at K >= 5 (shared memory
-// allows no more either: 112 KB per CTA), 3 below.
+// allows no more either: 112 KB per CTA), 3 below.  V8 (24 per level, K <= 4): 3 CTAs.
 __host__ __device__ constexpr int tk_min_blocks(int k, int lay) {
 #ifdef H2D_TK_MINBLOCKS
   return H2D_TK_MINBLOCKS;   // experiments only
 #else
-  return lay == LAY_AB4 ? ((k <= 4) ? 3 : 2) : ((k <= 5) ? 4 : 3);
+  return lay == LAY_AB4 ? ((k <= 4) ? 3 : 2) : (lay == LAY_V8 ? 3 : ((k <= 5) ? 4 : 3));
 #endif
 }
 template <int K, int LAY>
@@ -41,7 +41,8 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
   __shared__ bool cta_last;
   constexpr int W = Lay<LAY>::W;
   constexpr int STAGE_BYTES = TK_BR * W * 4;
-  constexpr int SMEM_RING = TK_WARPS * TK_STAGES * STAGE_BYTES;
+  constexpr int STAGES = tk_stages(LAY);
+  constexpr int SMEM_RING = TK_WARPS * STAGES * STAGE_BYTES;
   constexpr bool STRICT = ARITH != H2D_ARITH_FP32;
   // Converged earlier (or a conditional launch whose condition did not occur):
   // every CTA of every rank reads the same word and leaves; no flag is
@@ -52,7 +53,7 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
   if (*reinterpret_cast<const volatile uint32_t*>(a.fault) != 0u) return;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int task = (int)blockIdx.x * TK_WARPS + warp;
-  const uint32_t ring = smem_u32(smem) + warp * (TK_STAGES * STAGE_BYTES);
+  const uint32_t ring = smem_u32(smem) + warp * (STAGES * STAGE_BYTES);
   const uint32_t bars = smem_u32(smem) + SMEM_RING + warp * TK_STAGES * 8;
   if (STRICT && blockIdx.x == 0 && threadIdx.x == 0) a.strict_fb[(a.seq + 1u) % 3u] = 0u;
 
@@ -168,8 +169,13 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
         }
         if (need_slow) {
           // one generic instantiation (boundary selects and norm always compiled in): rare path
-          acc = run_task_v4<K, ARITH, false, true, XTR, false>(&tmap, a, a.dst, strip, r_lo, r_hi, ring, bars, lane,
-                                                               track, box0);
+          if constexpr (LAY == LAY_V8) {
+            acc = run_task_v8<K, ARITH, false, true, XTR, false>(&tmap, a, a.dst, strip, r_lo, r_hi, ring, bars, lane,
+                                                                 track, box0);
+          } else {
+            acc = run_task_v4<K, ARITH, false, true, XTR, false>(&tmap, a, a.dst, strip, r_lo, r_hi, ring, bars, lane,
+                                                                 track, box0);
+          }
           // feeds the next launch's decision, whichever way this task got here
           const bool bad = __any_sync(0xffffffffu, track >= STRICT_FAST_LIMIT);
           if (bad && lane == 0) atomicAdd(a.strict_fb + a.seq % 3u, 1u);
@@ -179,7 +185,7 @@ tk_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TkAr
       if (comm_edge && !(a.debug & 1)) {
         // every lane's stores of this chunk are ordered before the copies that read them back
         __syncwarp();
-        forward_task(a, strip, r_lo, r_hi, lane, ring, TK_STAGES * STAGE_BYTES);
+        forward_task(a, strip, r_lo, r_hi, lane, ring, STAGES * STAGE_BYTES);
       }
       if (comm_edge) {
         // Make this warp's peer stores visible system-wide, then count it in; the

@@ -11,6 +11,9 @@
 //
 //  * run_task_v4 (LAY_V4): 128-column strips, each lane owns 4 adjacent columns.
 //    Used by the strict (fp64-intermediate) modes, whose arithmetic is scalar.
+//  * run_task_v8 (LAY_V8): 256-column strips, each lane owns 8 adjacent columns; sweeps of
+//    at most 4 levels (the register state of 8 levels x 4 columns).  For the strict modes at
+//    k <= 4: 8 of 256 columns recomputed instead of 8 of 128, half the shuffles per point.
 //  * run_task_ab (LAY_AB2 / LAY_AB4): fp32 mode.  A strip is cut into a left
 //    half A and a right half B; a lane owns NC columns of A and the NC columns
 //    of B at the same offset, and keeps them PACKED as (A_j, B_j) in one 64-bit
@@ -32,21 +35,26 @@
 namespace h2d {
 
 constexpr int TK_BR = 6;         // rows per TMA box (a multiple of the 3-row register rotation)
-constexpr int TK_STAGES = 4;     // boxes in flight per warp
+constexpr int TK_STAGES = 4;     // boxes in flight per warp (see tk_stages)
 constexpr int TK_WARPS = 4;      // warps (tasks) per CTA
 constexpr int TK_WE_COLS = 32;   // columns forwarded per row and side: one full 128-byte line
 constexpr int TK_CW = 8;         // floats per row of a packed column-ghost buffer (= TK_KMAX)
 constexpr int TK_KMAX = 8;
 
-enum { LAY_V4 = 0, LAY_AB2 = 1, LAY_AB4 = 2, LAY_COUNT = 3 };
+enum { LAY_V4 = 0, LAY_AB2 = 1, LAY_AB4 = 2, LAY_V8 = 3, LAY_COUNT = 4 };
 template <int LAY> struct Lay;
 template <> struct Lay<LAY_V4>  { static constexpr int W = 128, NC = 4, HALF = 0; };
 template <> struct Lay<LAY_AB2> { static constexpr int W = 128, NC = 2, HALF = 64; };
 template <> struct Lay<LAY_AB4> { static constexpr int W = 256, NC = 4, HALF = 128; };
+template <> struct Lay<LAY_V8>  { static constexpr int W = 256, NC = 8, HALF = 0; };   // K <= 4 only
 
-__host__ __device__ constexpr int tk_strip_width(int lay) { return lay == LAY_AB4 ? 256 : 128; }
+__host__ __device__ constexpr int tk_strip_width(int lay) { return (lay == LAY_AB4 || lay == LAY_V8) ? 256 : 128; }
 __host__ __device__ constexpr int tk_stage_bytes(int lay) { return TK_BR * tk_strip_width(lay) * 4; }
-__host__ __device__ constexpr int tk_smem_ring(int lay) { return TK_WARPS * TK_STAGES * tk_stage_bytes(lay); }
+// boxes in flight per warp: V8's boxes are twice as wide and its sweeps at most 4 levels deep,
+// two of them keep the ring at the 12 KB per warp of the other 128-column layouts
+__host__ __device__ constexpr int tk_stages(int lay) { return lay == LAY_V8 ? 2 : TK_STAGES; }
+constexpr int TK_V8_KMAX = 4;
+__host__ __device__ constexpr int tk_smem_ring(int lay) { return TK_WARPS * tk_stages(lay) * tk_stage_bytes(lay); }
 constexpr int TK_SMEM_BARS = TK_WARPS * TK_STAGES * 8;
 __host__ __device__ constexpr int tk_smem_bytes(int lay, bool /*xtr*/ = false) {
   return tk_smem_ring(lay) + TK_SMEM_BARS;
@@ -560,6 +568,173 @@ __device__ __forceinline__ float run_task_v4(const CUtensorMap* tmap, const TkAr
 }
 
 // ============================================================================
+//                  task body, 8 adjacent columns per lane (K <= 4)
+// ============================================================================
+// The same pipeline as run_task_v4 on 256-column strips: a lane owns columns 8 l .. 8 l + 7 as
+// two float4 (lo, hi).  A sweep of K <= 4 levels needs a column margin of 4, so a strip stores
+// 248 of its 256 columns (120 of 128 in run_task_v4) and a lane shuffles twice per 8 points
+// instead of twice per 4; the register state — K levels x 3 rows x 8 columns — is what
+// run_task_v4 holds at K = 8.  Two 6-row boxes of 6 KB in flight per warp (tk_stages).
+struct Row8 { float4 lo, hi; };
+
+template <int K, int ARITH, bool IMM, bool FROZEN, bool NORM, bool FAST>
+__device__ __forceinline__ float run_task_v8(const CUtensorMap* tmap, const TkArgs& a, float* dst_base,
+                                             int strip, int r_lo, int r_hi, uint32_t ring, uint32_t bars, int lane,
+                                             uint32_t& track, int box0 = 0) {
+  static_assert(K <= TK_V8_KMAX, "the 8-column layout holds at most 4 levels");
+  constexpr bool TRACK = ARITH != H2D_ARITH_FP32;
+  constexpr int W = Lay<LAY_V8>::W;
+  constexpr int STAGES = tk_stages(LAY_V8);
+  constexpr int STAGE_BYTES = TK_BR * W * 4;
+  const Geo& g = a.g;
+  const int n_out = r_hi - r_lo;
+  const int own_lo = strip * a.wv;
+  const int vbase = (strip == a.n_strips - 1 && g.cols >= a.wv) ? ((g.cols - a.wv + 3) & ~3) : own_lo;
+  const int jbase = vbase - a.H;
+  const int j0 = jbase + lane * 8;
+  const int row0 = r_lo - K;
+  constexpr int LAG = 2 * K;
+  const int n_in = n_out + LAG;
+  const int n_blk = (n_in + TK_BR - 1) / TK_BR;
+  const int tc0 = g.halo_c + jbase;
+  const int tc1 = g.halo_r + row0;
+
+  // stored / owned elements of my 8 columns: inside the strip's valid window and the tile
+  int smask = 0, nmask = 0;
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const bool in = (lane * 8 + e >= a.H) && (lane * 8 + e < W - a.H);
+    if (in && (j0 + e) >= vbase && (j0 + e) < g.cols) smask |= 1 << e;
+    if (in && (j0 + e) >= own_lo && (j0 + e) < g.cols) nmask |= 1 << e;
+  }
+
+  bool act[8] = {true, true, true, true, true, true, true, true};
+  if (FROZEN) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int gy = g.y0 + j0 + e;
+      act[e] = gy >= g.ay_lo && gy <= g.ay_hi;
+    }
+  }
+
+  auto issue = [&](int b) {
+    const int s = (box0 + b) % STAGES;
+    const uint32_t bar = bars + s * 8;
+    mbar_expect_tx(bar, STAGE_BYTES);
+    tma_load_2d(ring + s * STAGE_BYTES, tmap, tc0, tc1 + b * TK_BR, bar);
+  };
+  if (lane == 0) {
+    const int pre = n_blk < STAGES ? n_blk : STAGES;
+    for (int b = 0; b < pre; ++b) issue(b);
+  }
+
+  Row8 st[K][3];
+#pragma unroll
+  for (int t = 0; t < K; ++t)
+#pragma unroll
+    for (int q3 = 0; q3 < 3; ++q3) st[t][q3].lo = st[t][q3].hi = make_float4(0.f, 0.f, 0.f, 0.f);
+
+  float acc = 0.f;
+  uint32_t trk = 0u;
+  int ro = -LAG;
+  float* q = dst_base + (int64_t)(g.halo_r + r_lo - LAG) * g.pitch + g.halo_c + j0;
+
+  auto row_step = [&](auto Ptag) {
+    constexpr int PH = decltype(Ptag)::value;
+    constexpr int iu = PH, ic = (PH + 1) % 3, id = (PH + 2) % 3;
+    Row8 fin, cprev;
+    cprev.lo = cprev.hi = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (TRACK) trk = umax4(umax4(trk, st[0][id].lo), st[0][id].hi);
+#pragma unroll
+    for (int t = 0; t < K; ++t) {
+      const Row8 up = st[t][iu];
+      const Row8 c = st[t][ic];
+      const Row8 down = st[t][id];
+      const float L = __shfl_up_sync(0xffffffffu, c.hi.w, 1);
+      const float Rn = __shfl_down_sync(0xffffffffu, c.lo.x, 1);
+      Row8 o;
+      o.lo = point4x<ARITH, IMM, FAST>(up.lo, c.lo, down.lo, L, c.hi.x, g);
+      o.hi = point4x<ARITH, IMM, FAST>(up.hi, c.hi, down.hi, c.lo.w, Rn, g);
+      if (FROZEN) {
+        const int gx = g.x0 + r_lo + ro + (K - 1 - t);
+        const bool ract = gx >= g.ax_lo && gx <= g.ax_hi;
+        o.lo.x = (ract && act[0]) ? o.lo.x : c.lo.x;
+        o.lo.y = (ract && act[1]) ? o.lo.y : c.lo.y;
+        o.lo.z = (ract && act[2]) ? o.lo.z : c.lo.z;
+        o.lo.w = (ract && act[3]) ? o.lo.w : c.lo.w;
+        o.hi.x = (ract && act[4]) ? o.hi.x : c.hi.x;
+        o.hi.y = (ract && act[5]) ? o.hi.y : c.hi.y;
+        o.hi.z = (ract && act[6]) ? o.hi.z : c.hi.z;
+        o.hi.w = (ract && act[7]) ? o.hi.w : c.hi.w;
+      }
+      if (TRACK) trk = umax4(umax4(trk, o.lo), o.hi);
+      if (t + 1 < K) {
+        st[t + 1][id] = o;
+      } else {
+        fin = o;
+        if (NORM) cprev = c;
+      }
+    }
+    if ((unsigned)ro < (unsigned)n_out) {
+      if ((smask & 0x0f) == 0x0f) {
+        *reinterpret_cast<float4*>(q) = fin.lo;
+      } else if (smask & 0x0f) {
+        if (smask & 1) q[0] = fin.lo.x;
+        if (smask & 2) q[1] = fin.lo.y;
+        if (smask & 4) q[2] = fin.lo.z;
+        if (smask & 8) q[3] = fin.lo.w;
+      }
+      if ((smask & 0xf0) == 0xf0) {
+        *reinterpret_cast<float4*>(q + 4) = fin.hi;
+      } else if (smask & 0xf0) {
+        if (smask & 16) q[4] = fin.hi.x;
+        if (smask & 32) q[5] = fin.hi.y;
+        if (smask & 64) q[6] = fin.hi.z;
+        if (smask & 128) q[7] = fin.hi.w;
+      }
+      if (NORM && nmask != 0) {
+        const float d[8] = {fin.lo.x - cprev.lo.x, fin.lo.y - cprev.lo.y, fin.lo.z - cprev.lo.z, fin.lo.w - cprev.lo.w,
+                            fin.hi.x - cprev.hi.x, fin.hi.y - cprev.hi.y, fin.hi.z - cprev.hi.z, fin.hi.w - cprev.hi.w};
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float de = ((nmask >> e) & 1) ? d[e] : 0.f;
+          // the same order of accumulation as a lane of run_task_v4 would not give the same
+          // partial sums anyway (other lanes own these columns there); the norm is reduced
+          // deterministically for a given layout, as everywhere
+          if (a.norm == H2D_NORM_L2SQ) acc = fmaf(de, de, acc);
+          else acc = fmax_nan(acc, fabsf(de));
+        }
+      }
+    }
+    q += g.pitch;
+    ++ro;
+  };
+
+#pragma unroll 1
+  for (int b = 0; b < n_blk; ++b) {
+    const int s = (box0 + b) % STAGES;
+    mbar_wait(bars + s * 8, (uint32_t)(((box0 + b) / STAGES) & 1));
+    const uint32_t sbase = ring + s * STAGE_BYTES + lane * 32;
+#pragma unroll 1
+    for (int rr = 0; rr < TK_BR; rr += 3) {
+      st[0][2].lo = lds128(sbase + rr * (W * 4));
+      st[0][2].hi = lds128(sbase + rr * (W * 4) + 16);
+      row_step(std::integral_constant<int, 0>{});
+      st[0][0].lo = lds128(sbase + (rr + 1) * (W * 4));
+      st[0][0].hi = lds128(sbase + (rr + 1) * (W * 4) + 16);
+      row_step(std::integral_constant<int, 1>{});
+      st[0][1].lo = lds128(sbase + (rr + 2) * (W * 4));
+      st[0][1].hi = lds128(sbase + (rr + 2) * (W * 4) + 16);
+      row_step(std::integral_constant<int, 2>{});
+    }
+    __syncwarp();
+    if (lane == 0 && b + STAGES < n_blk) issue(b + STAGES);
+  }
+  track = trk;
+  return acc;
+}
+
+// ============================================================================
 //               task body, fp32, two half-strips packed in f32x2
 // ============================================================================
 __device__ __forceinline__ float2 shfl2(float2 v, int src) {
@@ -751,8 +926,10 @@ __device__ __forceinline__ float run_task(const CUtensorMap* tmap, const TkArgs&
                                           uint32_t& track) {
   if constexpr (LAY == LAY_V4) {
     return run_task_v4<K, ARITH, IMM, FROZEN, NORM, FAST>(tmap, a, dst_base, strip, r_lo, r_hi, ring, bars, lane, track);
+  } else if constexpr (LAY == LAY_V8) {
+    return run_task_v8<K, ARITH, IMM, FROZEN, NORM, FAST>(tmap, a, dst_base, strip, r_lo, r_hi, ring, bars, lane, track);
   } else {
-    static_assert(ARITH == H2D_ARITH_FP32 || LAY == LAY_V4, "packed layouts are fp32 only");
+    static_assert(ARITH == H2D_ARITH_FP32, "packed layouts are fp32 only");
     track = 0u;
     return run_task_ab<K, LAY, IMM, FROZEN, NORM>(tmap, a, dst_base, strip, r_lo, r_hi, ring, bars, lane);
   }

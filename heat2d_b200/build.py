@@ -34,9 +34,9 @@ CUDA_SOURCES = ["basic_kernels.cu", "stencil_tk.cu", "stencil_flow.cu", "stencil
 # (object name, ARITH, LAY, XTR).  ARITH 0 fp32 / 1 strict / 2 strict-fma (heat2d.h);
 # LAY 0 v4 / 1 ab2 / 2 ab4 (csrc/tk_task.cuh); strict arithmetic exists in the v4 layout only.
 TK_INSTANCES = [(f"tk_a{a}_l{l}_x{x}", a, l, x)
-                for a, ls in ((0, (0, 1, 2)), (1, (0,)), (2, (0,))) for l in ls for x in (0, 1)]
+                for a, ls in ((0, (0, 1, 2)), (1, (0, 3)), (2, (0, 3))) for l in ls for x in (0, 1)]
 # defaults baked into the library (both can be overridden at run time, see stencil_tk.cu)
-TK_DEFAULTS = ["-DH2D_DEFAULT_FP32_LAYOUT=0", "-DH2D_DEFAULT_MIN_WAVES=2"]
+TK_DEFAULTS = ["-DH2D_DEFAULT_FP32_LAYOUT=0", "-DH2D_DEFAULT_MIN_WAVES=2", "-DH2D_DEFAULT_STRICT_SHALLOW_LAYOUT=3"]
 
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",

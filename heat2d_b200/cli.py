@@ -49,8 +49,9 @@ def build_parser() -> argparse.ArgumentParser:
                                          "a preset — what is fastest for the arithmetic and tile size (config.best_k)")
     ap.add_argument("--backend", choices=BACKENDS)
     ap.add_argument("--chunk-rows", type=int)
-    ap.add_argument("--layout", choices=["auto", "v4", "ab2", "ab4"],
-                    help="lane layout of the fp32 kernels (same bits; v4 is the measured best on B200)")
+    ap.add_argument("--layout", choices=["auto", "v4", "ab2", "ab4", "v8"],
+                    help="lane layout of the kernels (same bits): v4 | ab2 | ab4 for fp32 (v4 is the measured best on "
+                         "B200), v4 | v8 for strict arithmetic with -k <= 4")
     ap.add_argument("--team", choices=["on", "off"],
                     help="on: k >= 5 sweeps of single-GPU runs as cluster launches that share edge columns between "
                          "strips instead of recomputing them (same bits; pays off in strict arithmetic at >= 32768^2)")

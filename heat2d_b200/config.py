@@ -16,7 +16,7 @@ from ._native import ARITH, BOUNDARY, INIT, KMAX, NORM
 BACKENDS = ("fused", "single", "plain", "nccl-halo", "resident", "cpu")
 DUMPS = ("none", "prtdat", "rowmajor", "binary")
 CONV_MODES = ("exact", "fused-k")
-LAYOUTS = {"auto": 0, "v4": 1, "ab2": 2, "ab4": 3}
+LAYOUTS = {"auto": 0, "v4": 1, "ab2": 2, "ab4": 3, "v8": 4}
 
 
 class ConfigError(ValueError):
@@ -27,15 +27,16 @@ def best_k(arith: str, tile_points: int) -> int:
     """Sweep depth (time steps per launch) with the highest measured throughput on B200 for a
     tile of `tile_points` cells per GPU.  fp32: 8 — the kernel needs the 8-fold cut in HBM
     traffic.  Strict arithmetic is bound by instruction dispatch, not by HBM (DRAM 17 % busy at
-    k = 8), and k = 4 recomputes 8 of every 128 columns instead of 16 and fills its pipeline
-    in 8 rows instead of 16: strict-fma 1363 vs 1322 GLUP/s at 32768^2 (20 steps: 1361 vs 1294,
-    since 20 = 5 x 4 but 7 + 7 + 6), 1320 vs 1264 at 16384^2, 5215 vs 5010 on 2 x 2 GPUs — and
-    nothing on 8192 x 16384 tiles (1220 vs 1219), where twice the launches and halo exchanges
-    would only cost (profiles/r2/probe_strict-fma_*_ksweep.json, scaling_sweep_n4_ks.jsonl).
-    k = 3 and k = 2 are slower everywhere."""
+    k = 8); at k <= 4 the column margin is 4 instead of 8, the pipeline fills in 8 rows instead
+    of 16, 20 steps are 5 x 4 instead of 7 + 7 + 6, and the state of 4 levels leaves registers
+    for 8 columns per lane (the v8 layout: 8 of 256 columns recomputed).  strict-fma, GLUP/s,
+    k = 8 / k = 4 in v4 / k = 4 in v8: 32768^2 1322 / 1366 / 1438; 16384^2 1264 / 1320 / 1322;
+    8192 x 16384 (one tile of eight) 1219 / 1220 / 1280; 8192^2 1147 / 1169 / -; 2 x 2 GPUs
+    5010 / 5215 / - (profiles/r2/probe_strict-fma_*_ksweep.json, *_v8.json,
+    scaling_sweep_n4_ks.jsonl).  k = 3 and k = 2 are slower everywhere."""
     if arith == "fp32":
         return 8
-    return 4 if tile_points >= (1 << 28) else 8
+    return 4 if tile_points >= (1 << 27) else 8
 
 
 @dataclass
@@ -73,8 +74,9 @@ class HeatConfig:
     spin_timeout_s: float = 10.0
     dataflow: bool = False       # one dataflow launch per run of equal-k sweeps
                                  # (single tile, no convergence test; h2d_plan_run_dataflow)
-    layout: str = "auto"         # lane layout of the fp32 kernels: auto | v4 | ab2 | ab4 (csrc/tk_task.cuh);
-                                 # same bits, different speed; strict arithmetic always runs v4
+    layout: str = "auto"         # lane layout of the kernels (csrc/tk_task.cuh): auto | v4 | ab2 | ab4 (fp32) | v8
+                                 # (strict arithmetic with k <= 4; 8 columns per lane); same bits, different
+                                 # speed; a layout the arithmetic / depth does not have falls back to v4
     team: str = "off"            # on: sweeps of k >= 5 without neighbours / norm run as cluster launches whose
                                  # strips share their edge columns through shared memory (csrc/tk_team.cuh);
                                  # same bits; faster only in strict arithmetic on very large tiles

@@ -335,8 +335,8 @@ class Plan:
 
     @property
     def layout(self) -> str:
-        """Lane layout the plan's kernels use: 'v4', 'ab2' or 'ab4'."""
-        return {1: "v4", 2: "ab2", 3: "ab4"}.get(int(self._lib.h2d_plan_layout(self._h)), "?")
+        """Lane layout the plan's kernels use: 'v4', 'ab2', 'ab4' or 'v8'."""
+        return {1: "v4", 2: "ab2", 3: "ab4", 4: "v8"}.get(int(self._lib.h2d_plan_layout(self._h)), "?")
 
     @property
     def norm_ptr(self) -> int:

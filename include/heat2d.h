@@ -196,7 +196,9 @@ typedef struct h2d_plan_desc {
   /* Lane layout of the fp32 kernels (csrc/tk_task.cuh): 0 = library default
    * (H2D_FP32_LAYOUT=v4|ab2|ab4 overrides it), 1 = v4 (4 adjacent columns per lane,
    * 128-column strips), 2 = ab2 / 3 = ab4 (two half-strips packed in f32x2, 128- /
-   * 256-column strips).  Strict arithmetic always uses v4.  Results are bit-identical. */
+   * 256-column strips), 4 = v8 (8 adjacent columns per lane, 256-column strips; strict
+   * arithmetic, kmax <= 4 only).  Strict arithmetic uses v4 or v8.  A layout that does not exist
+   * for the arithmetic / depth falls back to the default.  Results are bit-identical.   */
   int32_t layout;
   /* != 0: k-step sweeps (k >= 5) of a plan without neighbours, launched without a norm, go out as
    * cluster launches whose strips exchange their edge columns through shared memory instead of

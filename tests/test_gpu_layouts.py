@@ -160,6 +160,81 @@ def test_strict_overflow_to_infinity_is_reproduced():
     assert same_bits_or_nan(got, want)
 
 
+# ------------------------------------------------- 8 columns per lane (strict arithmetic, k <= 4)
+@pytest.mark.parametrize("arith", ["strict", "strict-fma"])
+@pytest.mark.parametrize("k", [1, 2, 3, 4])
+@pytest.mark.parametrize("boundary", ["fixed", "ghost-ring"])
+def test_v8_layout_every_k_bit_exact(arith, k, boundary):
+    nx, ny = 150, 777      # several 248-column strips, a shifted last strip, odd sizes
+    u0 = rand_grid(nx, ny, k)
+    u0[:, 300:320] = 0.0
+    cfg = HeatConfig(nx=nx, ny=ny, steps=3 * k + 1, k=k, halo=8, boundary=boundary, arith=arith, chunk_rows=32,
+                     layout="v8")
+    s = Heat2DSolver(cfg, DEV).load(u0)
+    assert s.engines[0].plan.layout == "v8"
+    s.run()
+    assert np.array_equal(s.gather().numpy(), oracle(u0, 3 * k + 1, boundary, arith))
+
+
+@pytest.mark.parametrize("shape", [(10, 10), (80, 64), (640, 512), (1030, 2050), (97, 240), (64, 249), (33, 1000)])
+def test_v8_layout_on_reference_sizes(shape):
+    nx, ny = shape
+    u0 = K.cpu_initial_grid(nx, ny, "exact")
+    s = Heat2DSolver(HeatConfig(nx=nx, ny=ny, steps=50, k=4, arith="strict-fma", layout="v8"), DEV).initialize()
+    s.run()
+    assert np.array_equal(s.gather().numpy(), oracle(u0, 50, "fixed", "strict-fma"))
+
+
+@pytest.mark.parametrize("px,py", [(2, 2), (3, 1), (1, 3), (2, 4)])
+@pytest.mark.parametrize("boundary", ["fixed", "ghost-ring"])
+def test_v8_layout_virtual_tiles(px, py, boundary):
+    # halo forwarding (row bands, packed column ghosts, corners) behind the 8-column task body
+    for nx, ny in ((203, 517), (256, 2048)):
+        u0 = rand_grid(nx, ny, 9)
+        cfg = HeatConfig(nx=nx, ny=ny, steps=22, k=4, px=px, py=py, boundary=boundary, chunk_rows=16,
+                         arith="strict-fma", layout="v8")
+        s = Heat2DSolver(cfg, DEV).load(u0)
+        assert s.engines[0].plan.layout == "v8"
+        res = s.run()
+        assert res.steps_done == 22
+        assert np.array_equal(s.gather().numpy(), oracle(u0, 22, boundary, "strict-fma")), (nx, ny)
+
+
+@pytest.mark.parametrize("px,py", [(1, 1), (2, 2)])
+def test_v8_layout_convergence_and_fallback(px, py):
+    nx, ny = 48, 600
+    cfg = HeatConfig(nx=nx, ny=ny, steps=100000, k=4, px=px, py=py, boundary="ghost-ring", conv=True,
+                     interval=20, eps=0.1, arith="strict-fma", layout="v8")
+    s = Heat2DSolver(cfg, DEV).initialize()
+    res = s.run()
+    ref = K.cpu_initial_grid(nx, ny, "exact")
+    done, _ = K.cpu_run(ref, 100000, N.make_phys(0.1, 0.1, "ghost-ring", "strict-fma"), "l2sq", 20, 0.1)
+    assert res.converged and res.iterations == done
+    assert np.array_equal(s.gather().numpy(), ref)
+    # data outside the fast evaluation's domain: tasks are redone with the plain one
+    u0 = rand_grid(200, 900, 22) - np.float32(5e3)
+    u0[17, 33] = np.float32("inf")
+    s = Heat2DSolver(HeatConfig(nx=200, ny=900, steps=20, k=4, px=px, py=py, arith="strict-fma", chunk_rows=32,
+                                layout="v8"), DEV).load(u0)
+    s.run()
+    assert same_bits_or_nan(s.gather().numpy(), oracle(u0, 20, "fixed", "strict-fma"))
+
+
+def test_v8_layout_pipelined_solve_and_fallback_to_v4():
+    nx, ny = 1030, 2050
+    u0 = rand_grid(nx, ny, 4)
+    hin = torch.from_numpy(u0).pin_memory()
+    hout = torch.empty((nx, ny), dtype=torch.float32).pin_memory()
+    s = Heat2DSolver(HeatConfig(nx=nx, ny=ny, steps=22, k=4, arith="strict-fma", layout="v8"), DEV)
+    s.solve_pipelined(hin, hout, 22)
+    assert np.array_equal(hout.numpy(), oracle(u0, 22, "fixed", "strict-fma"))
+    # deeper sweeps and fp32 have no 8-column kernels: the plan falls back
+    s = Heat2DSolver(HeatConfig(nx=64, ny=300, steps=8, k=8, arith="strict-fma", layout="v8"), DEV).initialize()
+    assert s.engines[0].plan.layout == "v4"
+    s = Heat2DSolver(HeatConfig(nx=64, ny=300, steps=8, k=4, arith="fp32", layout="v8"), DEV).initialize()
+    assert s.engines[0].plan.layout in ("v4", "ab2", "ab4")
+
+
 # ------------------------------------------------------------------------ failure paths
 def test_linf_norm_propagates_nan():
     nx, ny = 64, 128

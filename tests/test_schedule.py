@@ -55,4 +55,5 @@ def test_best_k_follows_the_measurements():
     from heat2d_b200 import best_k
     assert best_k("fp32", 1 << 30) == 8 and best_k("fp32", 1 << 20) == 8
     assert best_k("strict-fma", 32768 * 32768) == 4 and best_k("strict", 16384 * 16384) == 4
-    assert best_k("strict-fma", 8192 * 16384) == 8      # an eighth of 32768^2: one tile of an 8-GPU run
+    assert best_k("strict-fma", 8192 * 16384) == 4      # an eighth of 32768^2: one tile of an 8-GPU run
+    assert best_k("strict-fma", 8192 * 8192) == 8
