@@ -3,7 +3,7 @@
 into profiles/ptxas_summary.txt.  The build writes its logs under heat2d_b200/_lib/obj/
 (untracked); this tool is the explicit step that turns them into a tracked record.
 
-    python tools/ptxas_report.py [--all]      # default: the K = 8 kernels only
+    python tools/ptxas_report.py [--all]      # default: the K = 8 kernels and the K = 4 strict ones
 """
 import re
 import subprocess
@@ -43,7 +43,8 @@ def main():
     for obj, mangled, regs, sp, smem in rows:
         name = names[mangled]
         name = re.sub(r"\(CUtensorMap_st.*", "", name).replace("h2d::", "").replace("void ", "")
-        if not want_all and "tk_" in name and not re.search(r"<8,", name):
+        # K = 8 everywhere, plus K = 4 of the strict modes (bench.py's headline runs there)
+        if not want_all and "tk_" in name and not re.search(r"<8,|<4, [12],", name):
             continue
         lines.append(f"{obj:16s} {name:58s} {regs:4d}  {sp[0]:4d}/{sp[1]:4d}/{sp[2]:4d}  {smem}")
     out = ROOT / "profiles" / "ptxas_summary.txt"
