@@ -153,10 +153,10 @@ def _make_solver(cfg, world, device, backend):
     return Heat2DSolver(cfg, device)
 
 
-def verify_small(a, cfg, world, rank, device, backend, ariths):
+def verify_small(a, cfg, world, rank, device, backend, ariths, ks=None):
     """Before anything is timed: a small random field through the SAME solver class, process
-    grid and k as the benchmark, compared bit for bit with the CPU oracle.  Returns a dict
-    {arith: bool}; identical on every rank."""
+    grid and k (per arithmetic: `ks`) as the benchmark, compared bit for bit with the CPU oracle.
+    Returns a dict {arith: bool}; identical on every rank."""
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -167,7 +167,8 @@ def verify_small(a, cfg, world, rank, device, backend, ariths):
     u0 = (rng.random((nx, ny), dtype=np.float32) * 100.0).astype(np.float32)
     res = {}
     for arith in ariths:
-        c = cfg.replace(nx=nx, ny=ny, steps=VERIFY_STEPS, arith=arith, conv=False, chunk_rows=0)
+        c = cfg.replace(nx=nx, ny=ny, steps=VERIFY_STEPS, arith=arith, conv=False, chunk_rows=0,
+                        k=(ks or {}).get(arith, cfg.k))
         s = _make_solver(c, world, device, backend)
         s.load(torch.from_numpy(u0))
         s.run(VERIFY_STEPS)
@@ -397,8 +398,20 @@ def main(argv=None):
 
     # ---- correctness first: a small case through the same classes, against the CPU oracle
     verified = None
+    k_other = (a.k or best_k(other, tile_pts)) if other else None
+    auto_k_fallback = False
     if not a.no_verify:
-        verified = verify_small(a, cfg, world, rank, device, backend, [a.arith] + ([other] if other else []))
+        ariths = [a.arith] + ([other] if other else [])
+        verified = verify_small(a, cfg, world, rank, device, backend, ariths, {a.arith: k, other: k_other})
+        if not all(verified.values()) and not a.k and backend == "fused" and (k != 8 or k_other not in (None, 8)):
+            # the depth best_k chose does not reproduce the oracle on this machine: fall back to
+            # k = 8 (4 columns per lane), the configuration every earlier record of this repository
+            # was measured with, and say so in the line
+            auto_k_fallback = True
+            k = 8
+            k_other = 8 if other else None
+            cfg = cfg.replace(k=8, halo=8)
+            verified = verify_small(a, cfg, world, rank, device, backend, ariths, {a.arith: 8, other: 8})
         if not all(verified.values()):
             if rank == 0:
                 print(json.dumps({"metric": METRIC, "impl": a.impl, "verified": False, "verify": verified,
@@ -425,7 +438,7 @@ def main(argv=None):
 
     extra = None
     if other is not None:
-        cfg2 = cfg.replace(arith=other, k=a.k or best_k(other, tile_pts))
+        cfg2 = cfg.replace(arith=other, k=k_other)
         s2 = _make_solver(cfg2, world, device, backend).initialize()
         r2, l2, c2 = _time_run(s2, a.steps, a.warmup, world, device, local)
         g2 = nx * ny * a.steps / r2.elapsed_s / 1e9
@@ -469,6 +482,7 @@ def main(argv=None):
                        "k": k, "backend": a.impl, "conv": bool(a.conv),
                        "l2": f"inputs larger than L2 ({nx * ny * 4 / world / 2**20:.0f} MiB per GPU per buffer vs 126 MiB)"},
             "clocks": clocks, "gpu_launches": launches, "impl": a.impl, "numa": numa,
+            "auto_k_fallback": auto_k_fallback,
             "verified": (None if verified is None else all(verified.values())),
             "verify": {"grid": list(VERIFY_GRID), "steps": VERIFY_STEPS, "bit_exact_vs_cpu_oracle": verified},
             "halo_wait_us_rank0": wait_us,
