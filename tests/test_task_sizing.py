@@ -55,3 +55,17 @@ def test_wide_strip_layout_fills_whole_waves_too():
     assert 200 <= R <= 2048 and (w <= round(w) + 1e-9 or w - int(w) > 0.85), (R, w)
     assert N.cuda().h2d_plan_strip_width(0, 3) == 256 and N.cuda().h2d_plan_strip_width(0, 1) == 128
     assert N.cuda().h2d_plan_strip_width(2, 3) == 128     # strict arithmetic always runs v4
+
+
+def test_eight_column_layout_of_the_strict_modes():
+    # v8: 256-column strips (248 stored), 12 resident warps; strict arithmetic, plans with kmax <= 4
+    lib = N.cuda()
+    assert lib.h2d_plan_strip_width(2, 4) == 256 and lib.h2d_plan_strip_width(1, 4) == 256
+    assert lib.h2d_plan_strip_width(0, 4) == 128            # fp32 has no 8-column kernels: the default layout
+    t = N.make_tile(32768, 32768, 0, 0, 32768, 32768, 8, 32, (32768 + 64 + 31) // 32 * 32)
+    R = lib.h2d_plan_chunk_rows_ex(C.byref(t), 4, 0, 2, 4)
+    ns = -(-32768 // 248)
+    w = -(-32768 // R) * ns / (148 * 12)
+    assert 200 <= R <= 2048 and (w <= round(w) + 1e-9 or w - int(w) > 0.85), (R, w)
+    # a deeper plan cannot use it: the sizing falls back to 128-column strips
+    assert lib.h2d_plan_chunk_rows_ex(C.byref(t), 8, 0, 2, 4) == lib.h2d_plan_chunk_rows_ex(C.byref(t), 8, 0, 2, 1)
